@@ -1,0 +1,222 @@
+/*
+ * mink_b200.h — C-ABI of the B200-native sparse-tensor convolution engine.
+ *
+ * This is the drop-in boundary for the MinkowskiEngine hot path.  Every entry
+ * point takes plain device pointers, sizes and a cudaStream_t (passed as
+ * void*), returns 0 on success or a non-zero MK_E* status, and never aborts;
+ * the message of the last failure on the calling thread is mk_last_error().
+ *
+ * Memory is owned by the caller (the Python host layer allocates everything
+ * with torch.empty, i.e. PyTorch's caching allocator — the reference default
+ * GPUMemoryAllocatorType.PYTORCH, MinkowskiCoordinateManager.py:46).  The
+ * library keeps no state besides the per-thread error string.
+ *
+ * Each group cites the reference interface it replaces (paths relative to the
+ * reference repo root).
+ *
+ * Coordinates are int32 rows [N, ncols] with the batch index first
+ * (utils/collation.py:89-91), ncols = D+1 <= 4.  Internally a row is packed
+ * into one 64-bit key: 16 bits batch (0..65535) + 3 x 16 bits signed
+ * coordinate (-32768..32767).  Out-of-range rows raise MK_ERANGE.
+ */
+#ifndef MINK_B200_H_
+#define MINK_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MK_OK 0
+#define MK_EINVAL 1   /* bad argument                                   */
+#define MK_ERANGE 2   /* coordinate outside the packable range          */
+#define MK_ECUDA 3    /* CUDA runtime error (message in mk_last_error)  */
+#define MK_EUNSUPPORTED 4
+#define MK_EFULL 5    /* hash table full (capacity too small)           */
+
+/* feature dtypes */
+#define MK_F32 0
+#define MK_F64 1
+#define MK_BF16 2
+#define MK_F16 3
+
+/* pooling modes (subset of PoolingMode, pybind/extern.hpp:706-732) */
+#define MK_POOL_SUM 0
+#define MK_POOL_AVG 1
+#define MK_POOL_MAX 2
+
+/* broadcast modes (BroadcastMode, pybind/extern.hpp:734-739) */
+#define MK_BCAST_ADD 0
+#define MK_BCAST_MUL 1
+
+const char *mk_last_error(void);
+int mk_version(void);
+/* 1 when the library was built with sm_100a tcgen05 kernels */
+int mk_has_tcgen05(void);
+
+/* ------------------------------------------------------------------------
+ * Coordinate hash.  Replaces CoordinateMapManager::insert_and_map and the
+ * cudf concurrent_unordered_map kernels behind it (pybind/extern.hpp:779;
+ * MinkowskiCoordinateManager.py:153-179).
+ *
+ * The table is `capacity` 16-byte slots {uint64 key, uint32 row, uint32 pad};
+ * capacity is a power of two from mk_hash_capacity(n) (>= 2n, <= 50% load).
+ * ---------------------------------------------------------------------- */
+int64_t mk_hash_capacity(int64_t n);
+/* bytes of scratch mk_map_insert needs for n rows */
+int64_t mk_insert_workspace_bytes(int64_t n);
+
+/*
+ * Insert n rows, deduplicate (first occurrence wins), and compact.
+ *   table        [capacity*16 B]  out: key -> compact row id
+ *   unique_index [n]   out: ascending original row of each unique coordinate
+ *   inverse_map  [n]   out: compact row id of every original row
+ *   coords_out   [n*ncols] out: coordinates of the unique rows, compact order
+ *   n_unique_dev [1]   out (device int64)
+ *   status_dev   [1]   out (device int32): 0 ok, MK_ERANGE, MK_EFULL
+ * Any of unique_index / inverse_map / coords_out may be NULL.
+ */
+int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
+                  int64_t capacity, int32_t *unique_index,
+                  int32_t *inverse_map, int32_t *coords_out, void *workspace,
+                  int64_t *n_unique_dev, int32_t *status_dev, void *stream);
+
+/* rows[i] = compact row id of query[i] in the table, or -1.
+ * Replaces thrust find_coordinate. */
+int mk_map_lookup(const void *table, int64_t capacity, const int32_t *query,
+                  int64_t nq, int ncols, int32_t *rows, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Coordinate generation.  Replaces manager.stride (extern.hpp:789), the
+ * expand_coordinates path of ConvolutionTransposeForwardGPU
+ * (extern.hpp:151-165) and origin maps (extern.hpp:790).
+ * ---------------------------------------------------------------------- */
+/* out[i, 1+d] = floor(in[i, 1+d] / new_stride[d]) * new_stride[d]; batch kept */
+int mk_coords_stride(const int32_t *in, int64_t n, int ncols,
+                     const int32_t *new_stride_host, int32_t *out,
+                     void *stream);
+/* out[i*K + k, :] = in[i, :] + (0, offsets[k, :]) ; offsets host [K, ncols-1] */
+int mk_coords_expand(const int32_t *in, int64_t n, int ncols,
+                     const int32_t *offsets_host, int K, int32_t *out,
+                     void *stream);
+/* out[i, :] = (in[i, 0], 0, 0, 0) */
+int mk_coords_origin(const int32_t *in, int64_t n, int ncols, int32_t *out,
+                     void *stream);
+
+/* ------------------------------------------------------------------------
+ * Pruning.  Replaces PruningForwardGPU / PruningBackwardGPU
+ * (extern.hpp:411-428; MinkowskiPruning.py:38-72).
+ * ---------------------------------------------------------------------- */
+int64_t mk_select_workspace_bytes(int64_t n);
+/* kept[j] = index of the j-th non-zero keep byte (order preserved) */
+int mk_select_flagged(const uint8_t *keep, int64_t n, int32_t *kept,
+                      void *workspace, int64_t *n_kept_dev, void *stream);
+/* dst[j, :] = src[idx[j], :]   (row_bytes per row, any dtype) */
+int mk_rows_gather(const void *src, const int32_t *idx, int64_t n_idx,
+                   int64_t row_bytes, void *dst, void *stream);
+/* dst[idx[j], :] = src[j, :]   (dst rows not listed are left untouched) */
+int mk_rows_scatter(const void *src, const int32_t *idx, int64_t n_idx,
+                    int64_t row_bytes, void *dst, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Kernel maps.  Replaces the count_kernel / preallocated_kernel_map_iteration
+ * pair behind CoordinateMapManager::kernel_map (extern.hpp:804;
+ * MinkowskiCoordinateManager.py:377-421).
+ *
+ * The engine's native form is the output-stationary neighbour table
+ *   nbr[k * ld + o] = input row hit by output row o under kernel offset k,
+ *                     or -1
+ * (k-major so that a tile of consecutive output rows reads/writes
+ * contiguous memory).  `offsets_host` is [K, ncols-1] in coordinate units
+ * (already multiplied by dilation * tensor_stride).
+ * ---------------------------------------------------------------------- */
+int mk_kmap_build(const int32_t *out_coords, int64_t n_out, int ncols,
+                  const void *in_table, int64_t in_capacity,
+                  const int32_t *offsets_host, int K, int32_t *nbr, int64_t ld,
+                  int64_t *counts_dev /* [K] pair counts, may be NULL */,
+                  void *stream);
+/* inverse table over input rows: inv[k*ld_in + nbr[k*ld+o]] = o, else -1 */
+int mk_kmap_invert(const int32_t *nbr, int64_t n_out, int64_t ld, int K,
+                   int32_t *inv, int64_t n_in, int64_t ld_in, void *stream);
+int64_t mk_kmap_pairs_workspace_bytes(int64_t n_out, int K);
+/* CSR export: for offset k, pairs [starts[k], starts[k+1]) ascending in o.
+ * Two calls with the same workspace: first with in_rows == NULL (counts ->
+ * starts_dev [K+1] int64; the caller reads starts_dev[K] and allocates), then
+ * with in_rows/out_rows sized >= starts[K] to fill them. */
+int mk_kmap_pairs(const int32_t *nbr, int64_t n_out, int64_t ld, int K,
+                  int64_t *starts_dev, int32_t *in_rows, int32_t *out_rows,
+                  void *workspace, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Convolution.  Replaces ConvolutionForwardGPU / ConvolutionBackwardGPU and
+ * the Transpose variants (extern.hpp:84-114,151-181): the matmul / matmul2
+ * gather-GEMM-scatter kernels.
+ *
+ *   y[o, :] = sum_k  x[nbr[k,o], :] @ W[k]          W: [K, Cin, Cout]
+ *
+ * mk_conv_fwd with (transpose_w = 1) computes x @ W[k]^T (W: [K, Cout_, Cin_]
+ * seen from the caller as [K, c_out_of_this_call... ]) and is the data
+ * gradient when called with the inverse table.  `kflip` != 0 reads offset
+ * K-1-k of the table for weight k (stride-1 same-map shortcut: the inverse
+ * table of a symmetric kernel is the table itself with offsets mirrored).
+ * bf16/f16 accumulate in fp32; f64 accumulates in f64.
+ * ---------------------------------------------------------------------- */
+int64_t mk_conv_workspace_bytes(int dtype, int64_t n_rows, int K, int c_in,
+                                int c_out);
+int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
+                int kflip, const int32_t *nbr, int64_t ld, int64_t n_out,
+                int K, int c_in, int c_out, void *y, void *workspace,
+                void *stream);
+/* dW[k] = sum_o x[nbr[k,o], :]^T  dy[o, :]    dW: [K, Cin, Cout] (dtype) */
+int mk_conv_wgrad(int dtype, const void *x, const void *dy,
+                  const int32_t *nbr, int64_t ld, int64_t n_out, int K,
+                  int c_in, int c_out, void *dw, void *workspace,
+                  void *stream);
+/* which implementation the last mk_conv_* call on this thread used:
+ * 0 = SIMT tiled kernel, 1 = tcgen05/TMEM kernel */
+int mk_conv_last_path(void);
+/* force the SIMT path (testing); returns previous value */
+int mk_conv_force_simt(int on);
+
+/* ------------------------------------------------------------------------
+ * Pooling / broadcast.  Replaces LocalPooling*GPU, GlobalPooling*GPU,
+ * Broadcast*GPU (extern.hpp:215-392).
+ * ---------------------------------------------------------------------- */
+/* y[o,:] = reduce_k x[nbr[k,o],:];  nnz[o] = #valid k (dtype of x);
+ * argmax [n_out*c] int32 (MK_POOL_MAX only, may be NULL otherwise) */
+int mk_pool_fwd(int dtype, int mode, const void *x, const int32_t *nbr,
+                int64_t ld, int64_t n_out, int K, int c, void *y, void *nnz,
+                int32_t *argmax, void *stream);
+/* dx (zero-initialised by the callee), via the inverse table (sum/avg) or the
+ * arg-max indices (max) */
+int mk_pool_bwd(int dtype, int mode, const void *dy, const void *nnz,
+                const int32_t *inv, int64_t ld_in, int64_t n_in, int K, int c,
+                const int32_t *argmax, int64_t n_out, void *dx, void *stream);
+/* scratch for the batch-segment kernels below */
+int64_t mk_segment_workspace_bytes(int dtype, int c, int64_t n_batch);
+/* batch-segment reduction: y[b,:] = reduce_{r: batch(r)=b} x[r,:].
+ * batch_of_row [n] int32, n_batch rows out; cnt [n_batch] (dtype) out;
+ * argmax [n_batch*c] for MK_POOL_MAX */
+int mk_global_pool_fwd(int dtype, int mode, const void *x,
+                       const int32_t *batch_of_row, int64_t n, int c,
+                       int64_t n_batch, void *y, void *cnt, int32_t *argmax,
+                       void *workspace, void *stream);
+int mk_global_pool_bwd(int dtype, int mode, const void *dy, const void *cnt,
+                       const int32_t *batch_of_row, int64_t n, int c,
+                       int64_t n_batch, const int32_t *argmax, void *dx,
+                       void *stream);
+/* y[r,:] = x[r,:] (+|*) g[batch(r),:] */
+int mk_broadcast_fwd(int dtype, int mode, const void *x, const void *g,
+                     const int32_t *batch_of_row, int64_t n, int c, void *y,
+                     void *stream);
+/* dx [n,c], dg [n_batch,c] */
+int mk_broadcast_bwd(int dtype, int mode, const void *x, const void *g,
+                     const void *dy, const int32_t *batch_of_row, int64_t n,
+                     int c, int64_t n_batch, void *dx, void *dg,
+                     void *workspace, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINK_B200_H_ */

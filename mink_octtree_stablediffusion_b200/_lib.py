@@ -1,0 +1,83 @@
+"""ctypes binding of libmink_b200.so (C-ABI: include/mink_b200.h).
+
+ctypes releases the GIL around every foreign call, which mirrors the
+`py::call_guard<py::gil_scoped_release>` on every reference op binding
+(pybind/extern.hpp:517-646).  There is no CPU fallback: if the library is
+missing or a call fails, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "lib" / "libmink_b200.so"
+
+MK_F32, MK_F64, MK_BF16, MK_F16 = 0, 1, 2, 3
+MK_POOL_SUM, MK_POOL_AVG, MK_POOL_MAX = 0, 1, 2
+MK_BCAST_ADD, MK_BCAST_MUL = 0, 1
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_i = C.c_int
+
+# name -> (restype, argtypes); must list every symbol include/mink_b200.h declares
+PROTOTYPES = {
+    "mk_last_error": (C.c_char_p, []),
+    "mk_version": (_i, []),
+    "mk_has_tcgen05": (_i, []),
+    "mk_hash_capacity": (_i64, [_i64]),
+    "mk_insert_workspace_bytes": (_i64, [_i64]),
+    "mk_map_insert": (_i, [_p, _i64, _i, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "mk_map_lookup": (_i, [_p, _i64, _p, _i64, _i, _p, _p]),
+    "mk_coords_stride": (_i, [_p, _i64, _i, _p, _p, _p]),
+    "mk_coords_expand": (_i, [_p, _i64, _i, _p, _i, _p, _p]),
+    "mk_coords_origin": (_i, [_p, _i64, _i, _p, _p]),
+    "mk_select_workspace_bytes": (_i64, [_i64]),
+    "mk_select_flagged": (_i, [_p, _i64, _p, _p, _p, _p]),
+    "mk_rows_gather": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "mk_rows_scatter": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "mk_kmap_build": (_i, [_p, _i64, _i, _p, _i64, _p, _i, _p, _i64, _p, _p]),
+    "mk_kmap_invert": (_i, [_p, _i64, _i64, _i, _p, _i64, _i64, _p]),
+    "mk_kmap_pairs_workspace_bytes": (_i64, [_i64, _i]),
+    "mk_kmap_pairs": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
+    "mk_conv_workspace_bytes": (_i64, [_i, _i64, _i, _i, _i]),
+    "mk_conv_fwd": (_i, [_i, _p, _p, _i, _i, _p, _i64, _i64, _i, _i, _i, _p, _p, _p]),
+    "mk_conv_wgrad": (_i, [_i, _p, _p, _p, _i64, _i64, _i, _i, _i, _p, _p, _p]),
+    "mk_conv_last_path": (_i, []),
+    "mk_conv_force_simt": (_i, [_i]),
+    "mk_pool_fwd": (_i, [_i, _i, _p, _p, _i64, _i64, _i, _i, _p, _p, _p, _p]),
+    "mk_pool_bwd": (_i, [_i, _i, _p, _p, _p, _i64, _i64, _i, _i, _p, _i64, _p, _p]),
+    "mk_segment_workspace_bytes": (_i64, [_i, _i, _i64]),
+    "mk_global_pool_fwd": (_i, [_i, _i, _p, _p, _i64, _i, _i64, _p, _p, _p, _p, _p]),
+    "mk_global_pool_bwd": (_i, [_i, _i, _p, _p, _p, _i64, _i, _i64, _p, _p, _p]),
+    "mk_broadcast_fwd": (_i, [_i, _i, _p, _p, _p, _i64, _i, _p, _p]),
+    "mk_broadcast_bwd": (_i, [_i, _i, _p, _p, _p, _p, _i64, _i, _i64, _p, _p, _p, _p]),
+}
+
+_lib = None
+
+
+def load(build_if_missing: bool = True) -> C.CDLL:
+    """Load (building in-tree first if needed) the C-ABI library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        if not build_if_missing:
+            raise RuntimeError(f"{LIB_PATH} is missing; run `python -m mink_octtree_stablediffusion_b200.build`")
+        from . import build as _build
+        _build.build_library()
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)          # AttributeError => symbol missing: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = load().mk_last_error()
+        raise RuntimeError(f"mink_b200 error {rc}: {msg.decode() if msg else '?'}")

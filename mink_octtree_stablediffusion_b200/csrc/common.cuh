@@ -1,0 +1,166 @@
+// Shared device/host helpers for the mink_b200 engine (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/mink_b200.h"
+
+namespace mk {
+
+// ---- error plumbing -------------------------------------------------------
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+
+#define MK_CHECK_ARG(cond, msg)                                                \
+  do {                                                                         \
+    if (!(cond)) {                                                             \
+      mk::set_error("%s: %s", __func__, msg);                                  \
+      return MK_EINVAL;                                                        \
+    }                                                                          \
+  } while (0)
+
+#define MK_CUDA(call)                                                          \
+  do {                                                                         \
+    cudaError_t e__ = (call);                                                  \
+    if (e__ != cudaSuccess) return mk::cuda_fail(e__, #call);                  \
+  } while (0)
+
+#define MK_LAUNCH_CHECK()                                                      \
+  do {                                                                         \
+    cudaError_t e__ = cudaGetLastError();                                      \
+    if (e__ != cudaSuccess) return mk::cuda_fail(e__, __func__);               \
+  } while (0)
+
+// batched single-CTA exclusive scan (hash.cu): row b of block_sums[batch][nblocks]
+// is scanned in place, its total written to total_dev[b]
+int scan_block_sums(int32_t *block_sums, int64_t nblocks, int batch,
+                    int64_t *total_dev, cudaStream_t st);
+
+inline int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) !=
+            cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// ---- coordinate keys --------------------------------------------------------
+// One coordinate row (b, x, y, z) -> 64-bit key.  Unused trailing axes are 0.
+// key = b << 48 | (x+32768) << 32 | (y+32768) << 16 | (z+32768).
+constexpr uint64_t kEmptyKey = 0xFFFFFFFFFFFFFFFFull;  // b=65535 is reserved
+
+struct __align__(16) Slot {
+  unsigned long long key;
+  uint32_t row;
+  uint32_t pad;
+};
+
+__host__ __device__ __forceinline__ bool coord_in_range(int b, int x, int y,
+                                                        int z) {
+  return b >= 0 && b < 65535 && x >= -32768 && x <= 32767 && y >= -32768 &&
+         y <= 32767 && z >= -32768 && z <= 32767;
+}
+
+__host__ __device__ __forceinline__ uint64_t pack_key(int b, int x, int y,
+                                                      int z) {
+  return ((uint64_t)(uint32_t)(b & 0xFFFF) << 48) |
+         ((uint64_t)(uint32_t)((x + 32768) & 0xFFFF) << 32) |
+         ((uint64_t)(uint32_t)((y + 32768) & 0xFFFF) << 16) |
+         (uint64_t)(uint32_t)((z + 32768) & 0xFFFF);
+}
+
+// 64-bit finaliser (splitmix64 / murmur3 fmix style)
+__host__ __device__ __forceinline__ uint32_t hash_key(uint64_t k) {
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return (uint32_t)k;
+}
+
+// read one coordinate row of ncols (<=4) int32 into b,x,y,z (missing = 0)
+__device__ __forceinline__ void load_coord(const int32_t *__restrict__ c,
+                                           int64_t i, int ncols, int &b,
+                                           int &x, int &y, int &z) {
+  if (ncols == 4) {
+    int4 v = __ldg(reinterpret_cast<const int4 *>(c) + i);
+    b = v.x; x = v.y; y = v.z; z = v.w;
+  } else {
+    const int32_t *p = c + i * ncols;
+    b = p[0];
+    x = ncols > 1 ? p[1] : 0;
+    y = ncols > 2 ? p[2] : 0;
+    z = 0;
+  }
+}
+
+__device__ __forceinline__ void store_coord(int32_t *__restrict__ c, int64_t i,
+                                            int ncols, int b, int x, int y,
+                                            int z) {
+  if (ncols == 4) {
+    reinterpret_cast<int4 *>(c)[i] = make_int4(b, x, y, z);
+  } else {
+    int32_t *p = c + i * ncols;
+    p[0] = b;
+    if (ncols > 1) p[1] = x;
+    if (ncols > 2) p[2] = y;
+  }
+}
+
+// probe the table for `key`; returns compact row or -1
+__device__ __forceinline__ int32_t table_find(const Slot *__restrict__ table,
+                                              uint32_t mask, uint64_t key) {
+  uint32_t h = hash_key(key) & mask;
+  while (true) {
+    // one 16-byte load: key + row together
+    const uint4 s = __ldg(reinterpret_cast<const uint4 *>(table + h));
+    const uint64_t k = ((uint64_t)s.y << 32) | s.x;
+    if (k == key) return (int32_t)s.z;
+    if (k == kEmptyKey) return -1;
+    h = (h + 1) & mask;
+  }
+}
+
+// ---- feature dtypes -----------------------------------------------------------
+template <typename T> struct Acc { using type = float; };
+template <> struct Acc<double> { using type = double; };
+
+template <typename T> __device__ __forceinline__ typename Acc<T>::type to_acc(T v) { return (typename Acc<T>::type)v; }
+template <> __device__ __forceinline__ float to_acc<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_acc<__half>(__half v) { return __half2float(v); }
+
+template <typename T, typename A> __device__ __forceinline__ T from_acc(A v) { return (T)v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_acc<__nv_bfloat16, float>(float v) { return __float2bfloat16(v); }
+template <> __device__ __forceinline__ __half from_acc<__half, float>(float v) { return __float2half(v); }
+
+inline int dtype_size(int dtype) {
+  switch (dtype) {
+    case MK_F32: return 4;
+    case MK_F64: return 8;
+    case MK_BF16: return 2;
+    case MK_F16: return 2;
+  }
+  return 0;
+}
+
+#define MK_DISPATCH_DTYPE(dtype, ...)                                          \
+  switch (dtype) {                                                             \
+    case MK_F32: { using T = float; __VA_ARGS__; break; }                      \
+    case MK_F64: { using T = double; __VA_ARGS__; break; }                     \
+    case MK_BF16: { using T = __nv_bfloat16; __VA_ARGS__; break; }             \
+    case MK_F16: { using T = __half; __VA_ARGS__; break; }                     \
+    default: mk::set_error("%s: unsupported dtype %d", __func__, dtype);       \
+             return MK_EUNSUPPORTED;                                           \
+  }
+
+}  // namespace mk

@@ -1,0 +1,106 @@
+// C-ABI entry points of the convolution group: pick the tcgen05/TMEM kernel
+// when the shape qualifies, otherwise the SIMT tiled kernel.  Both are CUDA;
+// there is no CPU path.
+#include "common.cuh"
+
+namespace mk {
+int conv_fwd_simt_dispatch(int dtype, const void *x, const void *w,
+                           int transpose_w, int kflip, const int32_t *nbr,
+                           int64_t ld, int64_t n_out, int K, int c_in,
+                           int c_out, void *y, cudaStream_t st);
+int conv_wgrad_simt_dispatch(int dtype, const void *x, const void *dy,
+                             const int32_t *nbr, int64_t ld, int64_t n_out,
+                             int K, int c_in, int c_out, void *dw,
+                             void *workspace, cudaStream_t st);
+// conv_tc.cu
+bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
+int64_t conv_fwd_tc_workspace(int K, int c_in, int c_out);
+int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w,
+                int kflip, const int32_t *nbr, int64_t ld, int64_t n_out,
+                int K, int c_in, int c_out, void *y, void *workspace,
+                cudaStream_t st);
+bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
+int64_t conv_wgrad_tc_workspace(int K, int c_in, int c_out);
+int conv_wgrad_tc(int dtype, const void *x, const void *dy,
+                  const int32_t *nbr, int64_t ld, int64_t n_out, int K,
+                  int c_in, int c_out, void *dw, void *workspace,
+                  cudaStream_t st);
+
+static thread_local int g_last_path = 0;
+static int g_force_simt = 0;
+}  // namespace mk
+
+using namespace mk;
+
+extern "C" {
+
+int mk_conv_last_path(void) { return g_last_path; }
+
+int mk_conv_force_simt(int on) {
+  const int prev = g_force_simt;
+  g_force_simt = on ? 1 : 0;
+  return prev;
+}
+
+int64_t mk_conv_workspace_bytes(int dtype, int64_t n_rows, int K, int c_in,
+                                int c_out) {
+  (void)n_rows;
+  int64_t b = 256;
+  // SIMT wgrad: fp32 accumulation buffer for 16-bit dtypes
+  if (dtype == MK_BF16 || dtype == MK_F16) b += (int64_t)K * c_in * c_out * 4;
+  b = std::max<int64_t>(b, conv_fwd_tc_workspace(K, c_in, c_out));
+  b = std::max<int64_t>(b, conv_wgrad_tc_workspace(K, c_in, c_out));
+  return b;
+}
+
+static int check_conv_args(int64_t ld, int64_t n_out, int K, int c_in,
+                           int c_out) {
+  MK_CHECK_ARG(K >= 1, "kernel volume must be >= 1");
+  MK_CHECK_ARG(c_in >= 1 && c_out >= 1, "channel counts must be >= 1");
+  MK_CHECK_ARG(n_out >= 0 && ld >= n_out, "ld must be >= n_out");
+  return MK_OK;
+}
+
+int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
+                int kflip, const int32_t *nbr, int64_t ld, int64_t n_out,
+                int K, int c_in, int c_out, void *y, void *workspace,
+                void *stream) {
+  int rc = check_conv_args(ld, n_out, K, c_in, c_out);
+  if (rc) return rc;
+  if (n_out == 0) return MK_OK;
+  MK_CHECK_ARG(x && w && nbr && y, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!g_force_simt && workspace &&
+      conv_fwd_tc_eligible(dtype, n_out, K, c_in, c_out)) {
+    g_last_path = 1;
+    return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, ld, n_out, K,
+                       c_in, c_out, y, workspace, st);
+  }
+  g_last_path = 0;
+  return conv_fwd_simt_dispatch(dtype, x, w, transpose_w, kflip, nbr, ld,
+                                n_out, K, c_in, c_out, y, st);
+}
+
+int mk_conv_wgrad(int dtype, const void *x, const void *dy,
+                  const int32_t *nbr, int64_t ld, int64_t n_out, int K,
+                  int c_in, int c_out, void *dw, void *workspace,
+                  void *stream) {
+  int rc = check_conv_args(ld, n_out, K, c_in, c_out);
+  if (rc) return rc;
+  MK_CHECK_ARG(dw, "null pointer");
+  MK_CHECK_ARG(n_out == 0 || (x && dy && nbr), "null pointer");
+  MK_CHECK_ARG(workspace || dtype == MK_F32 || dtype == MK_F64,
+               "workspace required for 16-bit dtypes");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!g_force_simt && workspace &&
+      conv_wgrad_tc_eligible(dtype, n_out, K, c_in, c_out)) {
+    g_last_path = 1;
+    return conv_wgrad_tc(dtype, x, dy, nbr, ld, n_out, K, c_in, c_out, dw,
+                         workspace, st);
+  }
+  g_last_path = 0;
+  return conv_wgrad_simt_dispatch(dtype, x, dy, nbr, ld, n_out, K, c_in,
+                                  c_out, dw, workspace, st);
+}
+
+}  // extern "C"
