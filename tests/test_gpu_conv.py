@@ -1,0 +1,142 @@
+"""GPU parity of the convolution kernels (through the C-ABI) against the CPU
+oracle.  fp32: <= 1e-5 relative; bf16: <= 1e-2 relative (north_star tolerances);
+fp64 checked to 1e-10."""
+import numpy as np
+import pytest
+import torch
+
+import abi
+from conftest import random_cloud
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_err(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def _setup(coords, out_coords, offs):
+    tin = abi.insert(coords)
+    nbr, ld, _ = abi.kmap_build(torch.from_numpy(out_coords).cuda(), tin["table"], tin["cap"], offs)
+    return nbr, ld, O.kernel_map(coords, out_coords, offs)
+
+
+TOL = {torch.float64: 1e-10, torch.float32: 1e-5, torch.bfloat16: 1e-2, torch.float16: 1e-2}
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("cin,cout", [(32, 64), (64, 64), (3, 32), (1, 4), (96, 48), (128, 128)])
+def test_conv_fwd_bwd_same_map(dtype, cin, cout):
+    c = O.sphere_surface(18, seed=1)
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    nbr, ld, ref = _setup(c, c, offs)
+    n = len(c)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, cin, generator=g, dtype=torch.float64)
+    w = torch.randn(27, cin, cout, generator=g, dtype=torch.float64) / np.sqrt(27 * cin)
+    dy = torch.randn(n, cout, generator=g, dtype=torch.float64)
+    xd, wd, dyd = (t.to(dtype).cuda() for t in (x, w, dy))
+    # oracle on the values the kernel actually sees (after rounding to dtype)
+    xr, wr, dyr = (t.double().cpu().numpy() for t in (xd, wd, dyd))
+    y_ref = O.conv_forward(xr, wr, ref, n)
+    gi_ref, gw_ref = O.conv_backward(xr, dyr, wr, ref)
+    tol = TOL[dtype]
+    y = abi.conv_fwd(xd, wd, nbr, ld, n)
+    assert rel_err(y.double().cpu().numpy(), y_ref) <= tol
+    # data gradient: symmetric same-map shortcut (table itself, offsets mirrored) ...
+    gi = abi.conv_fwd(dyd, wd, nbr, ld, n, transpose_w=1, kflip=1)
+    assert rel_err(gi.double().cpu().numpy(), gi_ref) <= tol
+    # ... and through the explicit inverse table
+    inv, ld_in = abi.kmap_invert(nbr, n, ld, 27, n)
+    gi2 = abi.conv_fwd(dyd, wd, inv, ld_in, n, transpose_w=1, kflip=0)
+    assert rel_err(gi2.double().cpu().numpy(), gi_ref) <= tol
+    gw = abi.conv_wgrad(xd, dyd, nbr, ld, n, 27)
+    assert rel_err(gw.double().cpu().numpy(), gw_ref) <= tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_conv_strided_and_transposed(dtype):
+    c = O.sphere_surface(22, seed=2)
+    s = O.stride_coords(c, [2, 2, 2])
+    tol = TOL[dtype]
+    g = torch.Generator().manual_seed(1)
+    # stride-2 3^3 conv: fine -> coarse
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    nbr, ld, ref = _setup(c, s, offs)
+    x = torch.randn(len(c), 64, generator=g).to(dtype).cuda()
+    w = (torch.randn(27, 64, 128, generator=g) / 40).to(dtype).cuda()
+    y = abi.conv_fwd(x, w, nbr, ld, len(s))
+    y_ref = O.conv_forward(x.double().cpu().numpy(), w.double().cpu().numpy(), ref, len(s))
+    assert rel_err(y.double().cpu().numpy(), y_ref) <= tol
+    dy = torch.randn(len(s), 128, generator=g).to(dtype).cuda()
+    gi_ref, gw_ref = O.conv_backward(x.double().cpu().numpy(), dy.double().cpu().numpy(), w.double().cpu().numpy(), ref)
+    inv, ld_in = abi.kmap_invert(nbr, len(s), ld, 27, len(c))
+    gi = abi.conv_fwd(dy, w, inv, ld_in, len(c), transpose_w=1)
+    assert rel_err(gi.double().cpu().numpy(), gi_ref) <= tol
+    gw = abi.conv_wgrad(x, dy, nbr, ld, len(s), 27)
+    assert rel_err(gw.double().cpu().numpy(), gw_ref) <= tol
+    # generative k2 s2 transpose: coarse -> 8 children
+    offs2 = O.kernel_offsets([2, 2, 2], [1, 1, 1])
+    fine = O.generative_coords(s, offs2)
+    tin = abi.insert(s)
+    nbr2, ld2, _ = abi.kmap_build(torch.from_numpy(fine).cuda(), tin["table"], tin["cap"], -offs2)
+    ref2 = O.kernel_map_transpose(s, fine, offs2)
+    xs = torch.randn(len(s), 128, generator=g).to(dtype).cuda()
+    w2 = (torch.randn(8, 128, 64, generator=g) / 12).to(dtype).cuda()
+    y2 = abi.conv_fwd(xs, w2, nbr2, ld2, len(fine))
+    y2_ref = O.conv_forward(xs.double().cpu().numpy(), w2.double().cpu().numpy(), ref2, len(fine))
+    assert rel_err(y2.double().cpu().numpy(), y2_ref) <= tol
+
+
+def test_conv_dense_grid_equals_conv3d():
+    import torch.nn.functional as F
+    S, cin, cout = 8, 16, 32
+    gidx = np.stack(np.meshgrid(np.arange(S), np.arange(S), np.arange(S), indexing="ij"), -1).reshape(-1, 3)
+    coords = np.concatenate([np.zeros((len(gidx), 1), np.int64), gidx], 1).astype(np.int32)
+    coords = coords[np.random.default_rng(0).permutation(len(coords))]
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    nbr, ld, _ = _setup(coords, coords, offs)
+    x = torch.randn(len(coords), cin, dtype=torch.float32)
+    w = torch.randn(27, cin, cout, dtype=torch.float32) / 20
+    y = abi.conv_fwd(x.cuda(), w.cuda(), nbr, ld, len(coords)).cpu()
+    dense = torch.zeros(1, cin, S, S, S)
+    dense[0, :, coords[:, 1], coords[:, 2], coords[:, 3]] = x.T
+    wt = w.reshape(3, 3, 3, cin, cout).permute(4, 3, 2, 1, 0).contiguous()
+    ref = F.conv3d(dense, wt, padding=1)[0][:, coords[:, 1], coords[:, 2], coords[:, 3]].T
+    assert rel_err(y.numpy(), ref.numpy()) <= 1e-5
+
+
+def test_conv_linearity_and_zero_rows_large():
+    """Size-independent properties at a larger size (oracle too slow): linearity
+    in x and in W, and rows with no neighbours give exactly zero."""
+    c = O.sphere_surface(120, seed=4)          # ~196k voxels
+    far = np.array([[0, 30000, 30000, 30000], [1, -30000, 5, 5]], np.int32)   # isolated voxels
+    c = np.concatenate([c, far]).astype(np.int32)
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, counts = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    g = torch.Generator().manual_seed(2)
+    x1 = torch.randn(n, 64, generator=g).cuda()
+    x2 = torch.randn(n, 64, generator=g).cuda()
+    w = (torch.randn(27, 64, 64, generator=g) / 40).cuda()
+    y1 = abi.conv_fwd(x1, w, nbr, ld, n)
+    y2 = abi.conv_fwd(x2, w, nbr, ld, n)
+    y12 = abi.conv_fwd(x1 + 2 * x2, w, nbr, ld, n)
+    assert rel_err((y1 + 2 * y2).cpu().numpy(), y12.cpu().numpy()) <= 1e-5
+    # isolated rows only see the centre offset
+    yc = x1[-2:] @ w[13]
+    assert rel_err(y1[-2:].cpu().numpy(), yc.cpu().numpy()) <= 1e-5
+    # <dy, conv(x)> == <dgrad(dy), x> == <wgrad(x, dy), W>   (adjointness)
+    dy = torch.randn(n, 64, generator=g).cuda()
+    gi = abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1)
+    gw = abi.conv_wgrad(x1, dy, nbr, ld, n, 27)
+    a = float((dy.double() * y1.double()).sum())
+    b = float((gi.double() * x1.double()).sum())
+    cc = float((gw.double() * w.double()).sum())
+    # the three inner products cancel heavily (|a| ~ sqrt(N)); compare on the scale of the summands
+    scale = float(dy.double().norm() * y1.double().norm())
+    assert abs(a - b) <= 1e-5 * scale and abs(a - cc) <= 1e-5 * scale
