@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py — north-star benchmark: MinkowskiConvolution fwd+bwd voxels/s on a
+1 M-voxel sphere-surface cloud, 3x3x3, 64->64 channels, bf16 (BASELINE.json).
+
+  python bench.py --gpus N --steps K --warmup W            (this engine, CUDA)
+  python bench.py --impl reference --gpus N --steps K ...  (CPU baseline arm)
+
+A "step" is one pass of the hot path over one batch of synthetic input:
+conv forward + data gradient + weight gradient with the kernel map cached (the
+reference caches it per (in,out,kernel) triple, docs/guides.md:7-17); the
+kernel-map build and hash insert are timed separately and reported beside it
+(`stages`).  N>1: one replica of the workload per GPU (weak scaling), the only
+collective is the NCCL all-reduce of the weight gradient.
+
+Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "sparse_conv_fwd_bwd_voxels_per_sec"
+UNIT = "voxels/s"
+R_FULL = 271          # sphere radius -> N ~ 1.00 M voxels
+C_IN = C_OUT = 64
+KS = 3
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d.get("bf16_tflops_sustained"),
+                    source="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, source="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([t.strip() for t in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i] == "Active" for r in self.rows)]
+        busy = [s for s in sm if s > 0.6 * (max(mx) if mx else 1)] or sm
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_cloud(R: int, seed: int, batch_index: int = 0) -> np.ndarray:
+    """G1 sphere-surface generator, int32 [N, 4], batch first."""
+    rng = np.random.default_rng(seed)
+    v = rng.normal(size=(40 * R * R, 3))
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    c = np.unique(np.floor(v * R + R + 1).astype(np.int32), axis=0)
+    return np.concatenate([np.full((len(c), 1), batch_index, np.int32), c], axis=1)
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: oracle/cpu_ref (C + OpenMP restatement of the ME CPU backend)
+# ---------------------------------------------------------------------------
+def cpu_sample(R: int, reps: int, seed: int = 0):
+    """Time conv fwd+bwd (kernel map cached, like the GPU step) on a sphere of
+    radius R, fp32 (the reference CPU backend has no bf16).  -> dict"""
+    from oracle import cpu_ref as CR
+    from oracle import oracle as O
+    c = make_cloud(R, seed)
+    n = len(c)
+    offs = O.kernel_offsets([KS] * 3, [1, 1, 1])
+    t0 = time.perf_counter()
+    cmap = CR.CoordMap(c)
+    t1 = time.perf_counter()
+    km = CR.KernelMap(cmap, c, offs)
+    t2 = time.perf_counter()
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((n, C_IN), dtype=np.float32)
+    w = (rng.standard_normal((KS ** 3, C_IN, C_OUT), dtype=np.float32) / np.sqrt(27 * C_IN)).astype(np.float32)
+    dy = rng.standard_normal((n, C_OUT), dtype=np.float32)
+    CR.conv_forward(x, w, km)                      # warm
+    ts = []
+    for _ in range(reps):
+        a = time.perf_counter()
+        CR.conv_forward(x, w, km)
+        CR.conv_backward(x, dy, w, km)
+        ts.append(time.perf_counter() - a)
+    return dict(n=n, P=int(km.counts.sum()), step_s=float(np.median(ts)), insert_s=t1 - t0, kmap_s=t2 - t1,
+                cores=CR.num_threads())
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    R = 96                                          # ~125 k voxels per step: a bounded sample of the workload
+    _ = cpu_sample(24, 1)                           # build/load + warm-up
+    times, info = [], None
+    for i in range(args.warmup + args.steps):
+        info = cpu_sample(R, 1, seed=i)
+        if i >= args.warmup:
+            times.append(info["step_s"])
+    t = float(np.mean(times))
+    val = info["n"] / t
+    sample = f"sphere R={R} ({info['n']} voxels, P={info['P']}), 3^3 {C_IN}->{C_OUT} fp32 fwd+bwd, kernel map cached"
+    line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
+            "config": {"workload": "north_star_conv_1M_k3_c64 (bounded sample per step)", "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": info["cores"], "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_engine(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this engine has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import MinkowskiEngine as ME
+    import MinkowskiEngineBackend._C as _C
+    from mink_octtree_stablediffusion_b200 import _lib
+    lib = _lib.load(build_if_missing=False)        # fail loudly if the CUDA library is missing
+    dev = torch.device("cuda", local)
+    pk = peaks()
+
+    R = args.radius
+    c = make_cloud(R, seed=rank)
+    n = len(c)
+    g = torch.Generator().manual_seed(1234 + rank)
+    coords_h = torch.from_numpy(c).pin_memory()
+    feats_h = torch.randn(n, C_IN, generator=g).to(torch.bfloat16).pin_memory()
+    dy = torch.randn(n, C_OUT, generator=g).to(torch.bfloat16).to(dev)
+    torch.manual_seed(0)
+    conv = ME.MinkowskiConvolution(C_IN, C_OUT, kernel_size=KS, dimension=3).to(torch.bfloat16).to(dev)
+    kg = conv.kernel_generator
+    coords_d = coords_h.to(dev)
+    feats_d = feats_h.to(dev)
+
+    # resident state: coordinate map + cached kernel map
+    st = ME.SparseTensor(feats_d, coords_d)
+    mgr, key = st.coordinate_manager._manager, st.coordinate_map_key
+    empty_off = torch.empty(0, dtype=torch.int32)
+    conv_args = (kg.kernel_size, kg.kernel_stride, kg.kernel_dilation, kg.region_type, empty_off)
+
+    def step_resident(ev=None):
+        if ev:
+            ev[0].record()
+        out = _C.ConvolutionForwardGPU(feats_d, conv.kernel, *conv_args, False, conv.convolution_mode, key, key, mgr)
+        if ev:
+            ev[1].record()
+        gi, gw = _C.ConvolutionBackwardGPU(feats_d, dy, conv.kernel, *conv_args, conv.convolution_mode, key, key, mgr)
+        if ev:
+            ev[2].record()
+        if world > 1:
+            dist.all_reduce(gw)                     # weight gradients only
+        return out, gi, gw
+
+    out, gi, gw = step_resident()
+    torch.cuda.synchronize()
+    kmap = next(iter(mgr._kmaps.values()))
+    P = int(kmap.counts.sum().item())
+    conv_path = int(lib.mk_conv_last_path())
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident timing ------------------------------------------
+    for _ in range(args.warmup):
+        step_resident()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    sync_all()
+    launches0 = int(lib.mk_launch_count())
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_start.record()
+    for i in range(args.steps):
+        step_resident(evs[i])
+    t_end.record()
+    sync_all()
+    launches = int(lib.mk_launch_count()) - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = t_start.elapsed_time(t_end)
+    fwd_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    bwd_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
+
+    # ---- end to end through the public ME API, host buffers ------------------
+    grad_h = torch.empty_like(conv.kernel, device="cpu").pin_memory()
+    chk_h = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def step_e2e():
+        coords_d.copy_(coords_h, non_blocking=True)
+        feats_d.copy_(feats_h, non_blocking=True)
+        conv.kernel.grad = None
+        x = feats_d.detach().requires_grad_(True)    # so that backward computes the data gradient too
+        s = ME.SparseTensor(x, coords_d)             # new manager: hash insert
+        o = conv(s)                                  # kernel-map build + forward
+        o.F.backward(dy)                             # dgrad + wgrad
+        if world > 1:
+            dist.all_reduce(conv.kernel.grad)
+        grad_h.copy_(conv.kernel.grad, non_blocking=True)
+        chk_h.copy_(o.F[:1024].float().sum().view(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()    # the step's result is on the host
+        return float(chk_h[0])
+
+    for _ in range(max(args.warmup, 3)):
+        step_e2e()
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_e2e()
+    e1.record()
+    sync_all()
+    ms_e2e = e0.elapsed_time(e1)
+
+    # ---- integer stages, timed alone (new map each iteration) ----------------
+    stage = {}
+    if rank == 0:
+        ins, kmb = [], []
+        for _ in range(5):
+            a, b, c2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            m2 = _C.CoordinateMapManagerGPU_c10()
+            a.record()
+            k2, _maps = m2.insert_and_map(coords_d, [1, 1, 1], "")
+            b.record()
+            m2.kernel_map(k2, k2, kg.kernel_size, kg.kernel_stride, kg.kernel_dilation, kg.region_type, empty_off,
+                          False, False)
+            c2.record()
+            torch.cuda.synchronize()
+            ins.append(a.elapsed_time(b))
+            kmb.append(b.elapsed_time(c2))
+        K = KS ** 3
+        stage = {"hash_insert_ms": float(np.median(ins)), "kmap_build_export_ms": float(np.median(kmb)),
+                 "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n + 8 * P)}
+
+    # ---- reduce over ranks -----------------------------------------------------
+    t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e, fwd_ms, bwd_ms = t.tolist()
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        value = n * world / (ms_step * 1e-3)
+        e2e_val = n * world / (ms_e2e / args.steps * 1e-3)
+        flops_pass = 2.0 * P * C_IN * C_OUT
+        tf = flops_pass / (fwd_ms * 1e-3) / 1e12
+        peak = pk["tf_sust"] or pk["tf_burst"]
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "north_star_conv_1M_k3_c64", "voxels_per_gpu": n, "pairs_per_gpu": P,
+                       "generator": f"sphere surface R={R}", "kernel": "3x3x3 stride 1", "channels": "64->64",
+                       "step": "conv fwd + dgrad + wgrad, kernel map cached", "parallelism": f"dp{world}",
+                       "l2": "working set (features, grads, neighbour table ~0.7 GB) exceeds the 126 MB L2"},
+            "roofline": {"bound": "tensor", "kernel": "conv forward (%s)" % ("tcgen05" if conv_path else "simt"),
+                         "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak, "traffic": None,
+                         "peak_source": pk["source"] + " (sustained bf16: kernel timed inside the step loop)",
+                         "useful_flops_per_launch": flops_pass},
+            "stages": {"conv_fwd_ms": fwd_ms, "conv_bwd_ms": bwd_ms,
+                       "fwd_bwd_useful_tflops": 3 * flops_pass / ((fwd_ms + bwd_ms) * 1e-3) / 1e12, **stage},
+            "e2e": {"value": e2e_val, "unit": UNIT,
+                    "h2d_bytes_per_step": int(coords_h.numel() * 4 + feats_h.numel() * 2),
+                    "d2h_bytes_per_step": int(grad_h.numel() * 2 + 4),
+                    "path": "pinned host coords+features -> ME.SparseTensor (hash insert) -> MinkowskiConvolution "
+                            "(kernel-map build + fwd) -> backward -> grad_kernel + checksum to host"},
+            "gpu_launches": launches, "clocks": clocks,
+        }
+        if stage:
+            line["stages"]["hash_insert_hbm_frac"] = stage["hash_insert_alg_bytes"] / (stage["hash_insert_ms"] * 1e-3) / 1e9 / pk["hbm"]
+            line["stages"]["kmap_hbm_frac"] = stage["kmap_alg_bytes"] / (stage["kmap_build_export_ms"] * 1e-3) / 1e9 / pk["hbm"]
+        if world == 1 and not args.no_cpu_baseline:
+            s = cpu_sample(96, 3)
+            line["cpu_baseline"] = {"value": s["n"] / s["step_s"], "unit": UNIT, "cores": s["cores"], "kind": "port",
+                                    "sample": f"sphere R=96 ({s['n']} voxels), 3^3 64->64 fp32 fwd+bwd, kernel map "
+                                              f"cached, median of 3 (oracle/cpu_ref.c, OpenMP)"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--radius", type=int, default=R_FULL, help="sphere radius of the synthetic cloud (271 -> 1 M voxels)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_engine(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -52,6 +52,8 @@ extern "C" {
 
 const char *mk_last_error(void);
 int mk_version(void);
+/* number of CUDA kernels this library has launched in the process so far */
+int64_t mk_launch_count(void);
 /* 1 when the library was built with sm_100a tcgen05 kernels */
 int mk_has_tcgen05(void);
 

@@ -25,6 +25,7 @@ _i = C.c_int
 PROTOTYPES = {
     "mk_last_error": (C.c_char_p, []),
     "mk_version": (_i, []),
+    "mk_launch_count": (_i64, []),
     "mk_has_tcgen05": (_i, []),
     "mk_hash_capacity": (_i64, [_i64]),
     "mk_insert_workspace_bytes": (_i64, [_i64]),

@@ -28,8 +28,13 @@ int cuda_fail(cudaError_t e, const char *what);
     if (e__ != cudaSuccess) return mk::cuda_fail(e__, #call);                  \
   } while (0)
 
+// every kernel launch of the library passes through MK_LAUNCH_CHECK, which also
+// feeds mk_launch_count() (bench.py's gpu_launches)
+extern unsigned long long g_launch_count;
+
 #define MK_LAUNCH_CHECK()                                                      \
   do {                                                                         \
+    ++mk::g_launch_count;                                                      \
     cudaError_t e__ = cudaGetLastError();                                      \
     if (e__ != cudaSuccess) return mk::cuda_fail(e__, __func__);               \
   } while (0)

@@ -20,6 +20,7 @@
 namespace mk {
 
 static thread_local char g_err[512] = "";
+unsigned long long g_launch_count = 0;
 
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -362,6 +363,7 @@ extern "C" {
 
 const char *mk_last_error(void) { return g_err; }
 int mk_version(void) { return 100; }
+int64_t mk_launch_count(void) { return (int64_t)g_launch_count; }
 
 int64_t mk_hash_capacity(int64_t n) {
   int64_t cap = 1024;
