@@ -150,6 +150,15 @@ int mk_kmap_pairs(const int32_t *nbr, int64_t n_out, int64_t ld, int K,
                   int64_t *starts_dev, int32_t *in_rows, int32_t *out_rows,
                   void *workspace, void *stream);
 
+/* Per 128-row tile of the table, a K-bit mask of the offsets that have at
+ * least one neighbour in the tile: mask[tile * W + k/32] bit (k%32), with
+ * W = mk_kmap_tile_mask_words(K).  The tensor-core convolution kernels use it
+ * to skip empty (tile, offset) pairs; it depends only on the kernel map, so it
+ * is built once and cached beside it. */
+int64_t mk_kmap_tile_mask_words(int K);
+int mk_kmap_tile_mask(const int32_t *nbr, int64_t n_rows, int64_t ld, int K,
+                      uint32_t *mask, void *stream);
+
 /* ------------------------------------------------------------------------
  * Convolution.  Replaces ConvolutionForwardGPU / ConvolutionBackwardGPU and
  * the Transpose variants (extern.hpp:84-114,151-181): the matmul / matmul2
@@ -163,16 +172,20 @@ int mk_kmap_pairs(const int32_t *nbr, int64_t n_out, int64_t ld, int K,
  * K-1-k of the table for weight k (stride-1 same-map shortcut: the inverse
  * table of a symmetric kernel is the table itself with offsets mirrored).
  * bf16/f16 accumulate in fp32; f64 accumulates in f64.
+ * `tile_mask` (mk_kmap_tile_mask of the SAME table) may be NULL: the tensor-
+ * core path then derives it into the workspace on every call.
  * ---------------------------------------------------------------------- */
 int64_t mk_conv_workspace_bytes(int dtype, int64_t n_rows, int K, int c_in,
                                 int c_out);
 int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
-                int kflip, const int32_t *nbr, int64_t ld, int64_t n_out,
+                int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                int64_t ld, int64_t n_out,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream);
 /* dW[k] = sum_o x[nbr[k,o], :]^T  dy[o, :]    dW: [K, Cin, Cout] (dtype) */
 int mk_conv_wgrad(int dtype, const void *x, const void *dy,
-                  const int32_t *nbr, int64_t ld, int64_t n_out, int K,
+                  const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
+                  int64_t n_out, int K,
                   int c_in, int c_out, void *dw, void *workspace,
                   void *stream);
 /* which implementation the last mk_conv_* call on this thread used:

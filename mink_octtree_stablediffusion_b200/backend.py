@@ -230,13 +230,15 @@ class _CoordMap:
 
 class _KernelMap:
     """Output-stationary neighbour table + lazily derived forms."""
-    __slots__ = ("nbr", "ld", "n_in", "n_out", "K", "counts", "_inv", "_pairs", "symmetric")
+    __slots__ = ("nbr", "ld", "n_in", "n_out", "K", "counts", "_inv", "_pairs", "symmetric", "_mask", "_imask")
 
     def __init__(self, nbr, ld, n_in, n_out, K, counts, symmetric):
         self.nbr, self.ld, self.n_in, self.n_out, self.K = nbr, ld, n_in, n_out, K
         self.counts = counts          # device int64 [K]
         self._inv = None
         self._pairs = None
+        self._mask = None             # tile masks of nbr / of the inverse table (lazy)
+        self._imask = None
         self.symmetric = symmetric    # inverse table == table with offsets mirrored
 
 

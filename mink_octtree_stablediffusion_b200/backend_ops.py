@@ -45,6 +45,33 @@ def _inverse_table(mgr, km: _KernelMap):
     return km._inv[0], km._inv[1], 0
 
 
+def _tile_mask(mgr, table: torch.Tensor, n_rows: int, ld: int, K: int) -> torch.Tensor:
+    """Per 128-row tile, the K-bit mask of offsets with at least one neighbour
+    (mk_kmap_tile_mask); lets the tensor-core kernels skip empty (tile, offset) pairs."""
+    lib = mgr._lib
+    W = int(lib.mk_kmap_tile_mask_words(K))
+    ntiles = (n_rows + 127) // 128
+    mask = torch.empty((max(ntiles, 1), W), dtype=torch.int32, device=table.device)
+    if n_rows > 0:
+        _lib.check(lib.mk_kmap_tile_mask(_ptr(table), n_rows, ld, K, _ptr(mask), _stream()))
+    return mask
+
+
+def _fwd_mask(mgr, km: _KernelMap) -> torch.Tensor:
+    if km._mask is None:
+        km._mask = _tile_mask(mgr, km.nbr, km.n_out, km.ld, km.K)
+    return km._mask
+
+
+def _inv_mask(mgr, km: _KernelMap) -> torch.Tensor:
+    if km.symmetric:
+        return _fwd_mask(mgr, km)
+    if km._imask is None:
+        inv, ld_in, _ = _inverse_table(mgr, km)
+        km._imask = _tile_mask(mgr, inv, km.n_in, ld_in, km.K)
+    return km._imask
+
+
 def _pairs(mgr, km: _KernelMap):
     """CSR export (starts[K+1] host list, in_rows, out_rows); pairs of an offset ascend in the out row."""
     if km._pairs is None:
@@ -148,14 +175,14 @@ def _workspace(lib, dtype_code, n, K, c_in, c_out, dev):
     return torch.empty(nbytes, dtype=torch.uint8, device=dev)
 
 
-def _conv_apply(mgr, x, w, transpose_w, kflip, table, ld, n_rows, K, c_in, c_out):
+def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in, c_out):
     lib = mgr._lib
     y = torch.empty((n_rows, c_out), dtype=x.dtype, device=x.device)
     if n_rows == 0:
         return y
     code = _dtype_code(x)
     ws = _workspace(lib, code, n_rows, K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_fwd(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), ld, n_rows, K,
+    _lib.check(lib.mk_conv_fwd(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld, n_rows, K,
                                c_in, c_out, _ptr(y), _ptr(ws), _stream()))
     return y
 
@@ -165,7 +192,8 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
     dw = torch.empty((km.K, c_in, c_out), dtype=x.dtype, device=x.device)
     code = _dtype_code(x)
     ws = _workspace(lib, code, km.n_out, km.K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(km.nbr), km.ld, km.n_out, km.K, c_in, c_out,
+    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(km.nbr), _ptr(_fwd_mask(mgr, km)), km.ld, km.n_out, km.K, c_in,
+                                 c_out,
                                  _ptr(dw), _ptr(ws), _stream()))
     return dw
 
@@ -203,7 +231,7 @@ def ConvolutionForwardGPU(in_feat, kernel, kernel_size, kernel_stride, kernel_di
     km = _kernel_map(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
                      False, False)
     _require(kernel.size(0) == km.K, "kernel.size(0) == kernel_volume")
-    return _conv_apply(mgr, in_feat, kernel.contiguous(), 0, 0, km.nbr, km.ld, km.n_out, km.K,
+    return _conv_apply(mgr, in_feat, kernel.contiguous(), 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K,
                        kernel.size(1), kernel.size(2))
 
 
@@ -215,7 +243,8 @@ def _conv_backward(in_feat, grad_out, kernel, km, mgr):
     kernel = kernel.contiguous()
     inv, ld_in, kflip = _inverse_table(mgr, km)
     # grad_in[i] = sum_k grad_out[inv[k, i]] @ W[k]^T
-    grad_in = _conv_apply(mgr, grad_out, kernel, 1, kflip, inv, ld_in, km.n_in, km.K, kernel.size(2), kernel.size(1))
+    grad_in = _conv_apply(mgr, grad_out, kernel, 1, kflip, inv, _inv_mask(mgr, km), ld_in, km.n_in, km.K,
+                          kernel.size(2), kernel.size(1))
     grad_w = _conv_wgrad(mgr, in_feat, grad_out, km, kernel.size(1), kernel.size(2))
     return grad_in, grad_w
 
@@ -238,7 +267,7 @@ def ConvolutionTransposeForwardGPU(in_feat, kernel, kernel_size, kernel_stride, 
     km = _kernel_map(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
                      True, False)
     _require(kernel.size(0) == km.K, "kernel.size(0) == kernel_volume")
-    return _conv_apply(mgr, in_feat, kernel.contiguous(), 0, 0, km.nbr, km.ld, km.n_out, km.K,
+    return _conv_apply(mgr, in_feat, kernel.contiguous(), 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K,
                        kernel.size(1), kernel.size(2))
 
 

@@ -14,17 +14,18 @@ int conv_wgrad_simt_dispatch(int dtype, const void *x, const void *dy,
                              void *workspace, cudaStream_t st);
 // conv_tc.cu
 bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
-int64_t conv_fwd_tc_workspace(int K, int c_in, int c_out);
+int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w,
-                int kflip, const int32_t *nbr, int64_t ld, int64_t n_out,
-                int K, int c_in, int c_out, void *y, void *workspace,
-                cudaStream_t st);
+                int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                int64_t ld, int64_t n_out, int K, int c_in, int c_out, void *y,
+                void *workspace, cudaStream_t st);
+// conv_wgrad_tc.cu
 bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
-int64_t conv_wgrad_tc_workspace(int K, int c_in, int c_out);
+int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_wgrad_tc(int dtype, const void *x, const void *dy,
-                  const int32_t *nbr, int64_t ld, int64_t n_out, int K,
-                  int c_in, int c_out, void *dw, void *workspace,
-                  cudaStream_t st);
+                  const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
+                  int64_t n_out, int K, int c_in, int c_out, void *dw,
+                  void *workspace, cudaStream_t st);
 
 static thread_local int g_last_path = 0;
 static int g_force_simt = 0;
@@ -44,12 +45,11 @@ int mk_conv_force_simt(int on) {
 
 int64_t mk_conv_workspace_bytes(int dtype, int64_t n_rows, int K, int c_in,
                                 int c_out) {
-  (void)n_rows;
   int64_t b = 256;
   // SIMT wgrad: fp32 accumulation buffer for 16-bit dtypes
   if (dtype == MK_BF16 || dtype == MK_F16) b += (int64_t)K * c_in * c_out * 4;
-  b = std::max<int64_t>(b, conv_fwd_tc_workspace(K, c_in, c_out));
-  b = std::max<int64_t>(b, conv_wgrad_tc_workspace(K, c_in, c_out));
+  b = std::max<int64_t>(b, conv_fwd_tc_workspace(n_rows, K, c_in, c_out));
+  b = std::max<int64_t>(b, conv_wgrad_tc_workspace(n_rows, K, c_in, c_out));
   return b;
 }
 
@@ -62,7 +62,8 @@ static int check_conv_args(int64_t ld, int64_t n_out, int K, int c_in,
 }
 
 int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
-                int kflip, const int32_t *nbr, int64_t ld, int64_t n_out,
+                int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                int64_t ld, int64_t n_out,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
@@ -73,8 +74,8 @@ int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
   if (!g_force_simt && workspace &&
       conv_fwd_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
-    return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, ld, n_out, K,
-                       c_in, c_out, y, workspace, st);
+    return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
+                       n_out, K, c_in, c_out, y, workspace, st);
   }
   g_last_path = 0;
   return conv_fwd_simt_dispatch(dtype, x, w, transpose_w, kflip, nbr, ld,
@@ -82,7 +83,8 @@ int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
 }
 
 int mk_conv_wgrad(int dtype, const void *x, const void *dy,
-                  const int32_t *nbr, int64_t ld, int64_t n_out, int K,
+                  const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
+                  int64_t n_out, int K,
                   int c_in, int c_out, void *dw, void *workspace,
                   void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
@@ -95,8 +97,8 @@ int mk_conv_wgrad(int dtype, const void *x, const void *dy,
   if (!g_force_simt && workspace &&
       conv_wgrad_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
-    return conv_wgrad_tc(dtype, x, dy, nbr, ld, n_out, K, c_in, c_out, dw,
-                         workspace, st);
+    return conv_wgrad_tc(dtype, x, dy, nbr, tile_mask, ld, n_out, K, c_in,
+                         c_out, dw, workspace, st);
   }
   g_last_path = 0;
   return conv_wgrad_simt_dispatch(dtype, x, dy, nbr, ld, n_out, K, c_in,

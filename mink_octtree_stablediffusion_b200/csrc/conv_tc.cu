@@ -1,11 +1,466 @@
-// placeholder, replaced below
+// Tensor-core (tcgen05 / TMEM) sparse convolution, forward and data gradient.
+//
+// Replaces the matmul<T,uint,TILE> gather-GEMM-scatter kernels behind
+// ConvolutionForwardGPU / ConvolutionBackwardGPU (pybind/extern.hpp:84-114;
+// SURVEY §2.3): all kernel offsets in ONE persistent launch, output-stationary,
+// accumulators in TMEM, no atomics.
+//
+//   y[o, n0:n0+NT] = sum_k  x[nbr[kk(k), o], :] @ B_k          (fp32 accumulate)
+//
+// CTA roles (320 threads, 1 CTA / SM, all 512 TMEM columns):
+//   warps 0-3  epilogue : tcgen05.ld accumulators -> bf16/f16 -> global
+//   warps 4-7  gather   : LDGSTS 16-byte chunks of the neighbour rows into a
+//                         ring of 128-row x 128-byte A stages (128B swizzle),
+//                         missing neighbours zero-filled
+//   warp  8    MMA      : one lane issues tcgen05.mma (M=128, N=NT, K=16)
+//   warp  9    weights  : one lane bulk-copies the pre-swizzled B image of each
+//                         (offset, channel chunk) into a 2-stage ring
+// A CTA owns "groups" of T 128-row output tiles whose accumulators live side by
+// side in one half of TMEM; the two halves ping-pong so the epilogue of one
+// group overlaps the main loop of the next.  Which (tile, offset) pairs have
+// any neighbour at all is known up front from the kernel map's tile mask, so
+// every role walks the same static schedule and empty pairs are skipped.
+#include <algorithm>
+
 #include "common.cuh"
+#include "sm100.cuh"
+
 namespace mk {
-bool conv_fwd_tc_eligible(int, int64_t, int, int, int) { return false; }
-int64_t conv_fwd_tc_workspace(int, int, int) { return 0; }
-int conv_fwd_tc(int, const void *, const void *, int, int, const int32_t *, int64_t, int64_t, int, int, int, void *, void *, cudaStream_t) { return MK_EUNSUPPORTED; }
-bool conv_wgrad_tc_eligible(int, int64_t, int, int, int) { return false; }
-int64_t conv_wgrad_tc_workspace(int, int, int) { return 0; }
-int conv_wgrad_tc(int, const void *, const void *, const int32_t *, int64_t, int64_t, int, int, int, void *, void *, cudaStream_t) { return MK_EUNSUPPORTED; }
+using namespace sm100;
+
+constexpr int kTileM = 128;
+constexpr int kStageBytes = kTileM * 128;  // one A stage: 128 rows x 64 16-bit channels
+constexpr int kNumThreadsTC = 320;
+constexpr int kMaxT = 4;                   // tiles per group (256 TMEM columns / NT)
+
+struct ConvTCParams {
+  const void *x;          // [n_in, c_in] 16-bit
+  const void *bpack;      // [nsplit][K][nchunk][NT rows x 128 B] pre-swizzled
+  const int32_t *nbr;     // [K, ld]
+  const uint32_t *mask;   // [ntiles, W]
+  void *y;                // [n_out, c_out]
+  int64_t ld, n_out;
+  int K, W, kflip;
+  int c_in, c_out, nchunk, NT, T;
+  int a_stages;
+  int64_t ngroups;
+  uint32_t idesc;
+};
+
+struct Ring {
+  int stage = 0;
+  uint32_t phase = 0;
+  __device__ __forceinline__ void advance(int n) {
+    if (++stage == n) { stage = 0; phase ^= 1; }
+  }
+};
+
+// B image of W for the MMA: per (split, k, chunk) NT rows (n) x 64 reduction
+// channels (128 B, K-major), 16-byte chunks XOR-swizzled with (n & 7).
+//   transpose == 0: B(n, c) = W[k][c][n0 + n]        W: [K, c_red, c_n]
+//   transpose == 1: B(n, c) = W[k][n0 + n][c]        W: [K, c_n, c_red]
+template <typename T>
+__global__ void k_pack_b(const T *__restrict__ w, int transpose, int K, int c_red, int c_n, int nchunk, int NT,
+                         int nsplit, T *__restrict__ out) {
+  const int64_t total = (int64_t)nsplit * K * nchunk * NT * 64;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int cc = (int)(e & 63);
+    int64_t r = e >> 6;
+    const int n = (int)(r % NT); r /= NT;
+    const int ch = (int)(r % nchunk); r /= nchunk;
+    const int k = (int)(r % K);
+    const int sp = (int)(r / K);
+    const int c = ch * 64 + cc;
+    const int ng = sp * NT + n;
+    T v = T(0.f);
+    if (c < c_red && ng < c_n)
+      v = transpose ? w[((size_t)k * c_n + ng) * c_red + c] : w[((size_t)k * c_red + c) * c_n + ng];
+    const size_t base = ((((size_t)sp * K + k) * nchunk + ch) * NT + n) * 64;
+    const int chunk16 = (cc >> 3) ^ (n & 7);
+    out[base + chunk16 * 8 + (cc & 7)] = v;
+  }
 }
-extern "C" int mk_has_tcgen05(void) { return 0; }
+
+// mask[tile*W + k/32] bit k%32 = any(nbr[k, 128*tile .. 128*tile+127] >= 0)
+__global__ void k_tile_mask(const int32_t *__restrict__ nbr, int64_t n_rows, int64_t ld, int K, int W,
+                            uint32_t *__restrict__ mask) {
+  const int64_t tile = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  extern __shared__ uint32_t s_mask[];
+  for (int i = threadIdx.x; i < W; i += blockDim.x) s_mask[i] = 0;
+  __syncthreads();
+  for (int k = warp; k < K; k += nwarp) {
+    const int32_t *row = nbr + (int64_t)k * ld + tile * kTileM;
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t o = tile * kTileM + j * 32 + lane;
+      any |= (o < n_rows) && (__ldg(row + j * 32 + lane) >= 0);
+    }
+    if (__any_sync(0xffffffffu, any) && lane == 0) atomicOr(&s_mask[k >> 5], 1u << (k & 31));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < W; i += blockDim.x) mask[tile * W + i] = s_mask[i];
+}
+
+template <typename T> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&v);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&v);
+}
+
+// T-bit mask over the tiles of a group: bit t set iff tile (tile0 + t) has any
+// neighbour under table offset kk
+__device__ __forceinline__ uint32_t group_bits(const ConvTCParams &p, int64_t tile0, int64_t ntiles, int kk) {
+  uint32_t bits = 0;
+  for (int t = 0; t < p.T; ++t) {
+    const int64_t tile = tile0 + t;
+    if (tile < ntiles) bits |= ((__ldg(p.mask + tile * p.W + (kk >> 5)) >> (kk & 31)) & 1u) << t;
+  }
+  return bits;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_constant__ ConvTCParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B-swizzle atoms
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int S = p.a_stages;
+  const uint32_t b_bytes = (uint32_t)p.NT * 128u;
+  uint8_t *a_ring = smem;
+  uint8_t *b_ring = a_ring + (size_t)S * kStageBytes;
+  uint64_t *bars = (uint64_t *)(b_ring + 2 * b_bytes);
+  uint64_t *a_full = bars, *a_empty = bars + S;
+  uint64_t *b_full = bars + 2 * S, *b_empty = b_full + 2;
+  uint64_t *t_full = b_empty + 2, *t_empty = t_full + 2;
+  uint32_t *tmem_slot = (uint32_t *)(t_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t ntiles = (p.n_out + kTileM - 1) / kTileM;
+  const int sp = blockIdx.y;
+  const int acc_stride = (p.NT + 31) & ~31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(&a_full[s], 32); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1);
+      mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 8) tmem_alloc_512(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 4) {
+    // ===================== epilogue =====================
+    int it = 0;
+    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
+      const int h = it & 1;
+      const int64_t tile0 = g * p.T;
+      mbar_wait(&t_full[h], (uint32_t)(it >> 1) & 1u);
+      tc_fence_after();
+      for (int t = 0; t < p.T; ++t) {
+        const int64_t tile = tile0 + t;
+        if (tile >= ntiles) break;
+        uint32_t touched = 0;
+        for (int wi = 0; wi < p.W; ++wi) touched |= __ldg(p.mask + tile * p.W + wi);
+        const int64_t row = tile * kTileM + warp * 32 + lane;
+        T *yrow = (T *)p.y + (size_t)row * p.c_out + (size_t)sp * p.NT;
+        const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * 256 + t * acc_stride);
+        for (int c0 = 0; c0 < p.NT; c0 += 16) {
+          uint32_t v[16];
+          if (touched) {
+            tmem_ld16(tbase + (uint32_t)c0, v);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = 0u;
+          }
+          if (row < p.n_out) {
+            uint4 o0, o1;
+            o0.x = pack2<T>(__uint_as_float(v[0]), __uint_as_float(v[1]));
+            o0.y = pack2<T>(__uint_as_float(v[2]), __uint_as_float(v[3]));
+            o0.z = pack2<T>(__uint_as_float(v[4]), __uint_as_float(v[5]));
+            o0.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
+            o1.x = pack2<T>(__uint_as_float(v[8]), __uint_as_float(v[9]));
+            o1.y = pack2<T>(__uint_as_float(v[10]), __uint_as_float(v[11]));
+            o1.z = pack2<T>(__uint_as_float(v[12]), __uint_as_float(v[13]));
+            o1.w = pack2<T>(__uint_as_float(v[14]), __uint_as_float(v[15]));
+            *reinterpret_cast<uint4 *>(yrow + c0) = o0;
+            *reinterpret_cast<uint4 *>(yrow + c0 + 8) = o1;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&t_empty[h]);
+    }
+  } else if (warp < 8) {
+    // ===================== gather producers =====================
+    const int w = warp - 4;
+    const uint32_t a_base = smem_u32(a_ring);
+    const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
+    const int c16 = lane & 7;              // 16-byte chunk inside the 128-byte row
+    const int rsub = lane >> 3;            // row inside a group of 4
+    int32_t cur[4] = {-1, -1, -1, -1}, nxt[4];
+    int64_t cur_e = 0;
+    int cur_ch = 0;
+    bool pending = false;
+    int64_t e = 0;
+
+    auto gather = [&](const int32_t(&idx)[4], int64_t ee, int ch) {
+      const int s = (int)(ee % S);
+      const uint32_t ph = (uint32_t)((ee / S) & 1);
+      mbar_wait(&a_empty[s], ph ^ 1u);
+      const uint32_t sbase = a_base + (uint32_t)s * kStageBytes;
+      const bool col_ok = (ch * 64 + c16 * 8) < p.c_in;
+      const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int r = 4 * i + rsub;
+        const int32_t ri = __shfl_sync(0xffffffffu, idx[i >> 3], r & 31);
+        const bool ok = col_ok && ri >= 0;
+        const uint32_t dst = sbase + (uint32_t)r * 128u + (uint32_t)((c16 ^ (r & 7)) << 4);
+        cp_async16(dst, ok ? (const void *)(xb + (size_t)ri * row_bytes) : p.x, ok ? 16u : 0u);
+      }
+      cp_async_arrive_noinc(&a_full[s]);
+    };
+
+    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+      const int64_t tile0 = g * p.T;
+      for (int k = 0; k < p.K; ++k) {
+        const int kk = p.kflip ? p.K - 1 - k : k;
+        const uint32_t bits = group_bits(p, tile0, ntiles, kk);
+        if (!bits) continue;
+        for (int ch = 0; ch < p.nchunk; ++ch) {
+          for (int t = 0; t < p.T; ++t) {
+            if (!((bits >> t) & 1u)) continue;
+            if ((int)(e & 3) == w) {
+              const int64_t row0 = (tile0 + t) * kTileM;
+              const int32_t *src = p.nbr + (int64_t)kk * p.ld + row0;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int64_t o = row0 + j * 32 + lane;
+                nxt[j] = o < p.n_out ? __ldg(src + j * 32 + lane) : -1;
+              }
+              if (pending) gather(cur, cur_e, cur_ch);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) cur[j] = nxt[j];
+              cur_e = e; cur_ch = ch; pending = true;
+            }
+            ++e;
+          }
+        }
+      }
+    }
+    if (pending) gather(cur, cur_e, cur_ch);
+  } else if (warp == 8) {
+    // ===================== MMA issuer =====================
+    const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
+    int64_t e = 0, bq = 0;
+    int it = 0;
+    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
+      const int h = it & 1;
+      const int64_t tile0 = g * p.T;
+      mbar_wait(&t_empty[h], ((uint32_t)(it >> 1) & 1u) ^ 1u);
+      tc_fence_after();
+      uint32_t fresh = 0xFFFFFFFFu;   // tiles whose accumulator has not been written in this group
+      for (int k = 0; k < p.K; ++k) {
+        const int kk = p.kflip ? p.K - 1 - k : k;
+        const uint32_t bits = group_bits(p, tile0, ntiles, kk);
+        if (!bits) continue;
+        for (int ch = 0; ch < p.nchunk; ++ch) {
+          const int bs = (int)(bq & 1);
+          mbar_wait(&b_full[bs], (uint32_t)(bq >> 1) & 1u);
+          const int nks = min(4, (p.c_in - ch * 64) >> 4);
+          for (int t = 0; t < p.T; ++t) {
+            if (!((bits >> t) & 1u)) continue;
+            const int s = (int)(e % S);
+            mbar_wait(&a_full[s], (uint32_t)((e / S) & 1));
+            fence_proxy_async_smem();
+            tc_fence_after();
+            if (lane == 0) {
+              const uint32_t d = tmem_base + (uint32_t)(h * 256 + t * acc_stride);
+              const uint32_t sa = a_base + (uint32_t)s * kStageBytes;
+              const uint32_t sb = b_base + (uint32_t)bs * b_bytes;
+              for (int ks = 0; ks < nks; ++ks) {
+                const uint64_t ad = smem_desc_sw128(sa + ks * 32, 16, 1024);
+                const uint64_t bd = smem_desc_sw128(sb + ks * 32, 16, 1024);
+                umma_f16(d, ad, bd, p.idesc, (((fresh >> t) & 1u) && ks == 0) ? 0u : 1u);
+              }
+              umma_commit(&a_empty[s]);
+            }
+            __syncwarp();
+            fresh &= ~(1u << t);
+            ++e;
+          }
+          if (lane == 0) umma_commit(&b_empty[bs]);
+          __syncwarp();
+          ++bq;
+        }
+      }
+      if (lane == 0) umma_commit(&t_full[h]);
+      __syncwarp();
+    }
+  } else {
+    // ===================== weight loader =====================
+    const uint32_t b_base = smem_u32(b_ring);
+    int64_t bq = 0;
+    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+      const int64_t tile0 = g * p.T;
+      for (int k = 0; k < p.K; ++k) {
+        const int kk = p.kflip ? p.K - 1 - k : k;
+        if (!group_bits(p, tile0, ntiles, kk)) continue;
+        for (int ch = 0; ch < p.nchunk; ++ch) {
+          const int bs = (int)(bq & 1);
+          mbar_wait(&b_empty[bs], ((uint32_t)(bq >> 1) & 1u) ^ 1u);
+          if (lane == 0) {
+            const uint8_t *src = (const uint8_t *)p.bpack + (((size_t)sp * p.K + k) * p.nchunk + ch) * b_bytes;
+            mbar_arrive_expect_tx(&b_full[bs], b_bytes);
+            bulk_g2s(b_base + (uint32_t)bs * b_bytes, src, b_bytes, &b_full[bs]);
+          }
+          __syncwarp();
+          ++bq;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc_fence_after();
+    tmem_dealloc_512(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+struct TCPlan {
+  int nsplit, NT, nchunk, T, W, a_stages;
+  size_t smem, bpack_bytes, mask_bytes;
+};
+
+static inline size_t align256s(size_t b) { return (b + 255) & ~(size_t)255; }
+
+static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPlan &pl) {
+  if (dtype != MK_BF16 && dtype != MK_F16) return false;
+  if (c_in < 16 || c_in % 16 || c_out < 16 || c_out % 16 || K < 1 || K > 128 || n_out < 1) return false;
+  int nsplit = (c_out + 255) / 256;
+  while (c_out % (16 * nsplit)) ++nsplit;
+  pl.nsplit = nsplit;
+  pl.NT = c_out / nsplit;
+  pl.nchunk = (c_in + 63) / 64;
+  const int acc_stride = (pl.NT + 31) & ~31;
+  pl.T = std::min(kMaxT, 256 / acc_stride);
+  pl.W = (K + 31) / 32;
+  const size_t b_bytes = (size_t)pl.NT * 128;
+  const size_t fixed = 1024 /*align slack*/ + 2 * b_bytes + 512 /*barriers*/;
+  const size_t budget = 227 * 1024;
+  int S = (int)((budget - fixed) / kStageBytes);
+  S = std::min(S, 12);
+  if (S < 3) return false;
+  pl.a_stages = S;
+  pl.smem = fixed + (size_t)S * kStageBytes;
+  pl.bpack_bytes = align256s((size_t)nsplit * K * pl.nchunk * b_bytes);
+  pl.mask_bytes = align256s((size_t)((n_out + kTileM - 1) / kTileM) * pl.W * 4);
+  return true;
+}
+
+bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) {
+  TCPlan pl;
+  return make_plan(dtype, n_out, K, c_in, c_out, pl);
+}
+
+int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
+  TCPlan pl;
+  if (!make_plan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return 0;
+  return (int64_t)(pl.bpack_bytes + pl.mask_bytes + 256);
+}
+
+int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint32_t *mask, cudaStream_t st) {
+  const int W = (K + 31) / 32;
+  const int64_t ntiles = (n_rows + kTileM - 1) / kTileM;
+  if (ntiles == 0) return MK_OK;
+  k_tile_mask<<<(unsigned)ntiles, 256, W * sizeof(uint32_t), st>>>(nbr, n_rows, ld, K, W, mask);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+template <typename T>
+static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const void *w, int transpose_w, int kflip,
+                             const int32_t *nbr, const uint32_t *tile_mask, int64_t ld, int64_t n_out, int K,
+                             int c_in, int c_out, void *y, void *workspace, cudaStream_t st) {
+  uint8_t *ws = (uint8_t *)workspace;
+  T *bpack = (T *)ws;
+  uint32_t *mask = (uint32_t *)(ws + pl.bpack_bytes);
+  {
+    const int64_t total = (int64_t)pl.nsplit * K * pl.nchunk * pl.NT * 64;
+    const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 8);
+    k_pack_b<T><<<blocks, 256, 0, st>>>((const T *)w, transpose_w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit,
+                                        bpack);
+    MK_LAUNCH_CHECK();
+  }
+  if (tile_mask == nullptr) {
+    int rc = tile_mask_launch(nbr, n_out, ld, K, mask, st);
+    if (rc) return rc;
+    tile_mask = mask;
+  }
+  ConvTCParams p;
+  p.x = x; p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y;
+  p.ld = ld; p.n_out = n_out; p.K = K; p.W = pl.W; p.kflip = kflip;
+  p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
+  p.a_stages = pl.a_stages;
+  const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
+  p.ngroups = (ntiles + pl.T - 1) / pl.T;
+  p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
+  static bool attr_set[2] = {false, false};
+  if (!attr_set[fmt]) {
+    MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[fmt] = true;
+  }
+  const int gx = (int)std::min<int64_t>(p.ngroups, std::max(1, num_sms() / pl.nsplit));
+  dim3 grid(gx, pl.nsplit);
+  k_conv_tc<T><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
+                const uint32_t *tile_mask, int64_t ld, int64_t n_out, int K, int c_in, int c_out, void *y,
+                void *workspace, cudaStream_t st) {
+  TCPlan pl;
+  if (!make_plan(dtype, n_out, K, c_in, c_out, pl)) {
+    set_error("conv_fwd_tc: shape not eligible");
+    return MK_EUNSUPPORTED;
+  }
+  if (dtype == MK_BF16)
+    return conv_fwd_tc_typed<__nv_bfloat16>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, K, c_in,
+                                            c_out, y, workspace, st);
+  return conv_fwd_tc_typed<__half>(pl, 0, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, K, c_in, c_out, y,
+                                   workspace, st);
+}
+
+// weight gradient on tensor cores: conv_wgrad_tc.cu
+}  // namespace mk
+
+extern "C" int mk_has_tcgen05(void) { return 1; }
+
+extern "C" int64_t mk_kmap_tile_mask_words(int K) { return (K + 31) / 32; }
+
+extern "C" int mk_kmap_tile_mask(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint32_t *mask,
+                                 void *stream) {
+  MK_CHECK_ARG(K >= 1 && ld >= n_rows, "bad K / ld");
+  if (n_rows == 0) return MK_OK;
+  MK_CHECK_ARG(nbr && mask, "null pointer");
+  return mk::tile_mask_launch(nbr, n_rows, ld, K, mask, (cudaStream_t)stream);
+}

@@ -86,7 +86,7 @@ def kmap_invert(nbr, n_out, ld, K, n_in):
     return inv, ld_in
 
 
-def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None):
+def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None, mask=None):
     lib = _lib.load()
     K = w.shape[0]
     c_in = x.shape[1]
@@ -95,16 +95,33 @@ def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None):
     y = torch.empty((n_out, c_out), dtype=x.dtype, device="cuda")
     ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
                      device="cuda")
-    _lib.check(lib.mk_conv_fwd(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), ld, n_out, K, c_in, c_out,
+    _lib.check(lib.mk_conv_fwd(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, K, c_in, c_out,
                                P(y), P(ws), S()))
     return y
 
 
-def conv_wgrad(x, dy, nbr, ld, n_out, K):
+def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None):
     lib = _lib.load()
     c_in, c_out = x.shape[1], dy.shape[1]
     dw = torch.empty((K, c_in, c_out), dtype=x.dtype, device="cuda")
     ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
                      device="cuda")
-    _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), ld, n_out, K, c_in, c_out, P(dw), P(ws), S()))
+    _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), P(mask), ld, n_out, K, c_in, c_out, P(dw), P(ws), S()))
     return dw
+
+
+def tile_mask(nbr, n_rows, ld, K):
+    lib = _lib.load()
+    W = int(lib.mk_kmap_tile_mask_words(K))
+    ntiles = (n_rows + 127) // 128
+    m = torch.empty((max(ntiles, 1), W), dtype=torch.int32, device="cuda")
+    _lib.check(lib.mk_kmap_tile_mask(P(nbr), n_rows, ld, K, P(m), S()))
+    return m[:ntiles]
+
+
+def last_path():
+    return int(_lib.load().mk_conv_last_path())
+
+
+def force_simt(on):
+    return int(_lib.load().mk_conv_force_simt(int(on)))
