@@ -174,18 +174,21 @@ int mk_kmap_tile_mask(const int32_t *nbr, int64_t n_rows, int64_t ld, int K,
  * bf16/f16 accumulate in fp32; f64 accumulates in f64.
  * `tile_mask` (mk_kmap_tile_mask of the SAME table) may be NULL: the tensor-
  * core path then derives it into the workspace on every call.
+ * `n_in` is the number of rows of x (table entries outside [0, n_in) count as
+ * missing).  The tensor-core path needs ld % 128 == 0 and 16-byte aligned
+ * x / nbr; other layouts are served by the SIMT kernels.
  * ---------------------------------------------------------------------- */
 int64_t mk_conv_workspace_bytes(int dtype, int64_t n_rows, int K, int c_in,
                                 int c_out);
 int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
                 int kflip, const int32_t *nbr, const uint32_t *tile_mask,
-                int64_t ld, int64_t n_out,
+                int64_t ld, int64_t n_out, int64_t n_in,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream);
 /* dW[k] = sum_o x[nbr[k,o], :]^T  dy[o, :]    dW: [K, Cin, Cout] (dtype) */
 int mk_conv_wgrad(int dtype, const void *x, const void *dy,
                   const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
-                  int64_t n_out, int K,
+                  int64_t n_out, int64_t n_in, int K,
                   int c_in, int c_out, void *dw, void *workspace,
                   void *stream);
 /* which implementation the last mk_conv_* call on this thread used:

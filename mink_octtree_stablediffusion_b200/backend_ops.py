@@ -182,7 +182,8 @@ def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in,
         return y
     code = _dtype_code(x)
     ws = _workspace(lib, code, n_rows, K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_fwd(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld, n_rows, K,
+    _lib.check(lib.mk_conv_fwd(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld, n_rows,
+                               x.size(0), K,
                                c_in, c_out, _ptr(y), _ptr(ws), _stream()))
     return y
 
@@ -192,7 +193,7 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
     dw = torch.empty((km.K, c_in, c_out), dtype=x.dtype, device=x.device)
     code = _dtype_code(x)
     ws = _workspace(lib, code, km.n_out, km.K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(km.nbr), _ptr(_fwd_mask(mgr, km)), km.ld, km.n_out, km.K, c_in,
+    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(km.nbr), _ptr(_fwd_mask(mgr, km)), km.ld, km.n_out, x.size(0), km.K, c_in,
                                  c_out,
                                  _ptr(dw), _ptr(ws), _stream()))
     return dw

@@ -17,15 +17,15 @@ bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
 int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w,
                 int kflip, const int32_t *nbr, const uint32_t *tile_mask,
-                int64_t ld, int64_t n_out, int K, int c_in, int c_out, void *y,
-                void *workspace, cudaStream_t st);
+                int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                int c_out, void *y, void *workspace, cudaStream_t st);
 // conv_wgrad_tc.cu
 bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
 int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_wgrad_tc(int dtype, const void *x, const void *dy,
                   const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
-                  int64_t n_out, int K, int c_in, int c_out, void *dw,
-                  void *workspace, cudaStream_t st);
+                  int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                  void *dw, void *workspace, cudaStream_t st);
 
 static thread_local int g_last_path = 0;
 static int g_force_simt = 0;
@@ -53,6 +53,12 @@ int64_t mk_conv_workspace_bytes(int dtype, int64_t n_rows, int K, int c_in,
   return b;
 }
 
+static bool tc_layout_ok(const void *x, const void *other, const int32_t *nbr,
+                         int64_t ld) {
+  return ld % 128 == 0 && ((uintptr_t)x & 15) == 0 &&
+         ((uintptr_t)other & 15) == 0 && ((uintptr_t)nbr & 15) == 0;
+}
+
 static int check_conv_args(int64_t ld, int64_t n_out, int K, int c_in,
                            int c_out) {
   MK_CHECK_ARG(K >= 1, "kernel volume must be >= 1");
@@ -63,19 +69,20 @@ static int check_conv_args(int64_t ld, int64_t n_out, int K, int c_in,
 
 int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
                 int kflip, const int32_t *nbr, const uint32_t *tile_mask,
-                int64_t ld, int64_t n_out,
+                int64_t ld, int64_t n_out, int64_t n_in,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
   if (rc) return rc;
+  MK_CHECK_ARG(n_in >= 0, "n_in must be >= 0");
   if (n_out == 0) return MK_OK;
-  MK_CHECK_ARG(x && w && nbr && y, "null pointer");
+  MK_CHECK_ARG(w && nbr && y && (x || n_in == 0), "null pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  if (!g_force_simt && workspace &&
+  if (!g_force_simt && workspace && n_in > 0 && tc_layout_ok(x, y, nbr, ld) &&
       conv_fwd_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
     return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
-                       n_out, K, c_in, c_out, y, workspace, st);
+                       n_out, n_in, K, c_in, c_out, y, workspace, st);
   }
   g_last_path = 0;
   return conv_fwd_simt_dispatch(dtype, x, w, transpose_w, kflip, nbr, ld,
@@ -84,21 +91,23 @@ int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
 
 int mk_conv_wgrad(int dtype, const void *x, const void *dy,
                   const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
-                  int64_t n_out, int K,
+                  int64_t n_out, int64_t n_in, int K,
                   int c_in, int c_out, void *dw, void *workspace,
                   void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
   if (rc) return rc;
+  MK_CHECK_ARG(n_in >= 0, "n_in must be >= 0");
   MK_CHECK_ARG(dw, "null pointer");
   MK_CHECK_ARG(n_out == 0 || (x && dy && nbr), "null pointer");
   MK_CHECK_ARG(workspace || dtype == MK_F32 || dtype == MK_F64,
                "workspace required for 16-bit dtypes");
   cudaStream_t st = (cudaStream_t)stream;
-  if (!g_force_simt && workspace &&
+  if (!g_force_simt && workspace && n_in > 0 && n_out > 0 &&
+      tc_layout_ok(x, dy, nbr, ld) &&
       conv_wgrad_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
-    return conv_wgrad_tc(dtype, x, dy, nbr, tile_mask, ld, n_out, K, c_in,
-                         c_out, dw, workspace, st);
+    return conv_wgrad_tc(dtype, x, dy, nbr, tile_mask, ld, n_out, n_in, K,
+                         c_in, c_out, dw, workspace, st);
   }
   g_last_path = 0;
   return conv_wgrad_simt_dispatch(dtype, x, dy, nbr, ld, n_out, K, c_in,

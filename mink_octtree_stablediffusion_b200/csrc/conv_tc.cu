@@ -7,31 +7,40 @@
 //
 //   y[o, n0:n0+NT] = sum_k  x[nbr[kk(k), o], :] @ B_k          (fp32 accumulate)
 //
-// CTA roles (320 threads, 1 CTA / SM, all 512 TMEM columns):
+// CTA roles (352 threads, 1 CTA / SM, all 512 TMEM columns):
 //   warps 0-3  epilogue : tcgen05.ld accumulators -> bf16/f16 -> global
-//   warps 4-7  gather   : LDGSTS 16-byte chunks of the neighbour rows into a
+//   warp  4    indices  : one lane bulk-copies the 128 neighbour-table entries
+//                         of every (tile, offset) into a ring in shared memory
+//   warps 5-8  gather   : LDGSTS 16-byte chunks of the neighbour rows into a
 //                         ring of 128-row x 128-byte A stages (128B swizzle),
-//                         missing neighbours zero-filled
-//   warp  8    MMA      : one lane issues tcgen05.mma (M=128, N=NT, K=16)
-//   warp  9    weights  : one lane bulk-copies the pre-swizzled B image of each
-//                         (offset, channel chunk) into a 2-stage ring
+//                         missing neighbours zero-filled; stages are dealt
+//                         round-robin to the four warps
+//   warp  9    MMA      : one lane issues tcgen05.mma (M=128, N=NT, K=16)
+//   warp  10   weights  : one lane bulk-copies the pre-swizzled B image of each
+//                         (offset, channel chunk) into a ring
 // A CTA owns "groups" of T 128-row output tiles whose accumulators live side by
 // side in one half of TMEM; the two halves ping-pong so the epilogue of one
 // group overlaps the main loop of the next.  Which (tile, offset) pairs have
 // any neighbour at all is known up front from the kernel map's tile mask, so
 // every role walks the same static schedule and empty pairs are skipped.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "sm100.cuh"
+#include "tmap.cuh"
 
 namespace mk {
 using namespace sm100;
 
 constexpr int kTileM = 128;
 constexpr int kStageBytes = kTileM * 128;  // one A stage: 128 rows x 64 16-bit channels
-constexpr int kNumThreadsTC = 320;
+constexpr int kNumThreadsTC = 352;
+constexpr int kGatherWarps = 4;
 constexpr int kMaxT = 4;                   // tiles per group (256 TMEM columns / NT)
+constexpr int kIdxSlots = 32;              // ring of 512-byte neighbour-index rows
+constexpr int kBStages = 4;                // weight-image ring
+constexpr int kMaxK = 128;
 
 struct ConvTCParams {
   const void *x;          // [n_in, c_in] 16-bit
@@ -39,19 +48,19 @@ struct ConvTCParams {
   const int32_t *nbr;     // [K, ld]
   const uint32_t *mask;   // [ntiles, W]
   void *y;                // [n_out, c_out]
-  int64_t ld, n_out;
+  int64_t ld, n_out, n_in;
   int K, W, kflip;
   int c_in, c_out, nchunk, NT, T;
   int a_stages;
-  int64_t ngroups;
+  int ngroups;
   uint32_t idesc;
 };
 
+// ring position: stage index + phase parity, advanced without division
 struct Ring {
-  int stage = 0;
-  uint32_t phase = 0;
-  __device__ __forceinline__ void advance(int n) {
-    if (++stage == n) { stage = 0; phase ^= 1; }
+  uint32_t stage = 0, phase = 0;
+  __device__ __forceinline__ void advance(uint32_t n) {
+    if (++stage == n) { stage = 0; phase ^= 1u; }
   }
 };
 
@@ -114,30 +123,41 @@ template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) 
   return *reinterpret_cast<uint32_t *>(&v);
 }
 
-// T-bit mask over the tiles of a group: bit t set iff tile (tile0 + t) has any
-// neighbour under table offset kk
-__device__ __forceinline__ uint32_t group_bits(const ConvTCParams &p, int64_t tile0, int64_t ntiles, int kk) {
-  uint32_t bits = 0;
-  for (int t = 0; t < p.T; ++t) {
-    const int64_t tile = tile0 + t;
-    if (tile < ntiles) bits |= ((__ldg(p.mask + tile * p.W + (kk >> 5)) >> (kk & 31)) & 1u) << t;
+// Per-role copy of a group's schedule: sched[k] = T-bit mask of the group's
+// tiles that have any neighbour under the table offset used by weight k.
+// Called by a whole (converged) warp.
+__device__ __forceinline__ void fill_sched(uint8_t *sched, const ConvTCParams &p, int64_t tile0, int64_t ntiles,
+                                           int lane) {
+  __syncwarp();
+  for (int k = lane; k < p.K; k += 32) {
+    const int kk = p.kflip ? p.K - 1 - k : k;
+    uint32_t bits = 0;
+    for (int t = 0; t < p.T; ++t) {
+      const int64_t tile = tile0 + t;
+      if (tile < ntiles) bits |= ((__ldg(p.mask + tile * p.W + (kk >> 5)) >> (kk & 31)) & 1u) << t;
+    }
+    sched[k] = (uint8_t)bits;
   }
-  return bits;
+  __syncwarp();
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_constant__ ConvTCParams p) {
+__global__ void __launch_bounds__(kNumThreadsTC, 1)
+k_conv_tc(const __grid_constant__ ConvTCParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B-swizzle atoms
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  const int S = p.a_stages;
+  const uint32_t S = (uint32_t)p.a_stages;
   const uint32_t b_bytes = (uint32_t)p.NT * 128u;
   uint8_t *a_ring = smem;
   uint8_t *b_ring = a_ring + (size_t)S * kStageBytes;
-  uint64_t *bars = (uint64_t *)(b_ring + 2 * b_bytes);
-  uint64_t *a_full = bars, *a_empty = bars + S;
-  uint64_t *b_full = bars + 2 * S, *b_empty = b_full + 2;
-  uint64_t *t_full = b_empty + 2, *t_empty = t_full + 2;
+  int32_t *idx_ring = (int32_t *)(b_ring + kBStages * b_bytes);
+  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * kTileM);   // 4 role copies x kMaxK
+  uint64_t *bars = (uint64_t *)(sched_all + 7 * kMaxK);
+  uint64_t *a_full = bars, *a_empty = a_full + S;
+  uint64_t *b_full = a_empty + S, *b_empty = b_full + kBStages;
+  uint64_t *i_full = b_empty + kBStages, *i_empty = i_full + kIdxSlots;
+  uint64_t *t_full = i_empty + kIdxSlots, *t_empty = t_full + 2;
   uint32_t *tmem_slot = (uint32_t *)(t_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -146,14 +166,13 @@ __global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_const
   const int acc_stride = (p.NT + 31) & ~31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(&a_full[s], 32); mbar_init(&a_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1);
-      mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4);
-    }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 32); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)p.nchunk); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
     fence_barrier_init();
   }
-  if (warp == 8) tmem_alloc_512(tmem_slot);
+  if (warp == 9) tmem_alloc_512(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -161,11 +180,11 @@ __global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_const
 
   if (warp < 4) {
     // ===================== epilogue =====================
-    int it = 0;
-    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
-      const int h = it & 1;
-      const int64_t tile0 = g * p.T;
-      mbar_wait(&t_full[h], (uint32_t)(it >> 1) & 1u);
+    uint32_t it = 0;
+    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
+      const uint32_t h = it & 1u;
+      const int64_t tile0 = (int64_t)g * p.T;
+      mbar_wait(&t_full[h], (it >> 1) & 1u);
       tc_fence_after();
       for (int t = 0; t < p.T; ++t) {
         const int64_t tile = tile0 + t;
@@ -203,108 +222,135 @@ __global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_const
       __syncwarp();
       if (lane == 0) mbar_arrive(&t_empty[h]);
     }
-  } else if (warp < 8) {
-    // ===================== gather producers =====================
-    const int w = warp - 4;
-    const uint32_t a_base = smem_u32(a_ring);
-    const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
-    const int c16 = lane & 7;              // 16-byte chunk inside the 128-byte row
-    const int rsub = lane >> 3;            // row inside a group of 4
-    int32_t cur[4] = {-1, -1, -1, -1}, nxt[4];
-    int64_t cur_e = 0;
-    int cur_ch = 0;
-    bool pending = false;
-    int64_t e = 0;
-
-    auto gather = [&](const int32_t(&idx)[4], int64_t ee, int ch) {
-      const int s = (int)(ee % S);
-      const uint32_t ph = (uint32_t)((ee / S) & 1);
-      mbar_wait(&a_empty[s], ph ^ 1u);
-      const uint32_t sbase = a_base + (uint32_t)s * kStageBytes;
-      const bool col_ok = (ch * 64 + c16 * 8) < p.c_in;
-      const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const int r = 4 * i + rsub;
-        const int32_t ri = __shfl_sync(0xffffffffu, idx[i >> 3], r & 31);
-        const bool ok = col_ok && ri >= 0;
-        const uint32_t dst = sbase + (uint32_t)r * 128u + (uint32_t)((c16 ^ (r & 7)) << 4);
-        cp_async16(dst, ok ? (const void *)(xb + (size_t)ri * row_bytes) : p.x, ok ? 16u : 0u);
-      }
-      cp_async_arrive_noinc(&a_full[s]);
-    };
-
-    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
-      const int64_t tile0 = g * p.T;
+  } else if (warp == 4) {
+    // ===================== neighbour-index prefetch =====================
+    // one 512-byte row of the table per (offset, tile) -> idx ring; the channel
+    // chunks of a stage reuse the same indices, so the gather warp re-reads them
+    uint8_t *sched = sched_all + 0 * kMaxK;
+    const uint32_t i_base = smem_u32(idx_ring);
+    Ring ir;
+    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+      const int64_t tile0 = (int64_t)g * p.T;
+      fill_sched(sched, p, tile0, ntiles, lane);
       for (int k = 0; k < p.K; ++k) {
-        const int kk = p.kflip ? p.K - 1 - k : k;
-        const uint32_t bits = group_bits(p, tile0, ntiles, kk);
+        const uint32_t bits = sched[k];
         if (!bits) continue;
-        for (int ch = 0; ch < p.nchunk; ++ch) {
-          for (int t = 0; t < p.T; ++t) {
-            if (!((bits >> t) & 1u)) continue;
-            if ((int)(e & 3) == w) {
-              const int64_t row0 = (tile0 + t) * kTileM;
-              const int32_t *src = p.nbr + (int64_t)kk * p.ld + row0;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const int64_t o = row0 + j * 32 + lane;
-                nxt[j] = o < p.n_out ? __ldg(src + j * 32 + lane) : -1;
-              }
-              if (pending) gather(cur, cur_e, cur_ch);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) cur[j] = nxt[j];
-              cur_e = e; cur_ch = ch; pending = true;
-            }
-            ++e;
+        const int kk = p.kflip ? p.K - 1 - k : k;
+        for (int t = 0; t < p.T; ++t) {
+          if (!((bits >> t) & 1u)) continue;
+          mbar_wait(&i_empty[ir.stage], ir.phase ^ 1u);
+          if (lane == 0) {
+            const int32_t *src = p.nbr + (int64_t)kk * p.ld + (tile0 + t) * kTileM;
+            mbar_arrive_expect_tx(&i_full[ir.stage], kTileM * 4);
+            bulk_g2s(i_base + ir.stage * (kTileM * 4), src, kTileM * 4, &i_full[ir.stage]);
           }
+          __syncwarp();
+          ir.advance(kIdxSlots);
         }
       }
     }
-    if (pending) gather(cur, cur_e, cur_ch);
-  } else if (warp == 8) {
-    // ===================== MMA issuer =====================
-    const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
-    int64_t e = 0, bq = 0;
-    int it = 0;
-    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
-      const int h = it & 1;
-      const int64_t tile0 = g * p.T;
-      mbar_wait(&t_empty[h], ((uint32_t)(it >> 1) & 1u) ^ 1u);
-      tc_fence_after();
-      uint32_t fresh = 0xFFFFFFFFu;   // tiles whose accumulator has not been written in this group
+  } else if (warp < 5 + kGatherWarps) {
+    // ===================== gather producers (LDGSTS) =====================
+    // lane = (rsub, c16): instruction i of a stage moves 16-byte chunk c16 of tile
+    // rows rsub*32 + i, i.e. four 128-byte feature rows per warp instruction
+    const int w = warp - 5;
+    uint8_t *sched = sched_all + (1 + w) * kMaxK;
+    const uint32_t a_base = smem_u32(a_ring);
+    const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
+    const int c16 = lane & 7, rsub = lane >> 3;
+    Ring ir, ar;
+    uint32_t e = 0;
+    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+      const int64_t tile0 = (int64_t)g * p.T;
+      fill_sched(sched, p, tile0, ntiles, lane);
       for (int k = 0; k < p.K; ++k) {
-        const int kk = p.kflip ? p.K - 1 - k : k;
-        const uint32_t bits = group_bits(p, tile0, ntiles, kk);
+        const uint32_t bits = sched[k];
         if (!bits) continue;
+        Ring irt = ir;
         for (int ch = 0; ch < p.nchunk; ++ch) {
-          const int bs = (int)(bq & 1);
-          mbar_wait(&b_full[bs], (uint32_t)(bq >> 1) & 1u);
-          const int nks = min(4, (p.c_in - ch * 64) >> 4);
+          irt = ir;
+          const bool col_ok = (ch * 64 + c16 * 8) < p.c_in;
+          const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
           for (int t = 0; t < p.T; ++t) {
             if (!((bits >> t) & 1u)) continue;
-            const int s = (int)(e % S);
-            mbar_wait(&a_full[s], (uint32_t)((e / S) & 1));
-            fence_proxy_async_smem();
-            tc_fence_after();
-            if (lane == 0) {
-              const uint32_t d = tmem_base + (uint32_t)(h * 256 + t * acc_stride);
-              const uint32_t sa = a_base + (uint32_t)s * kStageBytes;
-              const uint32_t sb = b_base + (uint32_t)bs * b_bytes;
-              for (int ks = 0; ks < nks; ++ks) {
-                const uint64_t ad = smem_desc_sw128(sa + ks * 32, 16, 1024);
-                const uint64_t bd = smem_desc_sw128(sb + ks * 32, 16, 1024);
-                umma_f16(d, ad, bd, p.idesc, (((fresh >> t) & 1u) && ks == 0) ? 0u : 1u);
+            if ((e & (kGatherWarps - 1)) == (uint32_t)w) {
+              mbar_wait(&i_full[irt.stage], irt.phase);
+              const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + irt.stage * kTileM + rsub * 32);
+              int4 iv[8];
+#pragma unroll
+              for (int q = 0; q < 8; ++q) iv[q] = ip[q];
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&i_empty[irt.stage]);
+              mbar_wait(&a_empty[ar.stage], ar.phase ^ 1u);
+              const uint32_t sbase = a_base + ar.stage * kStageBytes;
+              const int64_t o0 = (tile0 + t) * kTileM + rsub * 32;
+              const int64_t lim = p.n_out - o0;     // rows of this lane's 32 that exist
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const int32_t ri = (i & 3) == 0 ? iv[i >> 2].x : (i & 3) == 1 ? iv[i >> 2].y
+                                   : (i & 3) == 2 ? iv[i >> 2].z : iv[i >> 2].w;
+                const uint32_t r = (uint32_t)(rsub * 32 + i);
+                const bool ok = col_ok && (uint32_t)ri < (uint32_t)p.n_in && i < lim;
+                const uint32_t dst = sbase + r * 128u + (uint32_t)((c16 ^ (i & 7)) << 4);
+                cp_async16(dst, ok ? (const void *)(xb + (size_t)ri * row_bytes) : p.x, ok ? 16u : 0u);
               }
-              umma_commit(&a_empty[s]);
+              cp_async_arrive_noinc(&a_full[ar.stage]);
             }
-            __syncwarp();
-            fresh &= ~(1u << t);
+            irt.advance(kIdxSlots);
+            ar.advance(S);
             ++e;
           }
-          if (lane == 0) umma_commit(&b_empty[bs]);
+        }
+        ir = irt;
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer =====================
+    uint8_t *sched = sched_all + 5 * kMaxK;
+    const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
+    // descriptor template: SBO = 1024 B (8-row atoms), LBO = 16 B (unused for one
+    // 128-byte K atom), version 1, SWIZZLE_128B; the start address is added per MMA
+    const uint64_t desc0 = smem_desc_sw128(0, 16, 1024);
+    Ring ar, br;
+    uint32_t it = 0;
+    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
+      const uint32_t h = it & 1u;
+      const int64_t tile0 = (int64_t)g * p.T;
+      fill_sched(sched, p, tile0, ntiles, lane);
+      mbar_wait(&t_empty[h], ((it >> 1) & 1u) ^ 1u);
+      tc_fence_after();
+      uint32_t fresh = 0xFu;   // tiles whose accumulator has not been written in this group
+      for (int k = 0; k < p.K; ++k) {
+        const uint32_t bits = sched[k];
+        if (!bits) continue;
+        for (int ch = 0; ch < p.nchunk; ++ch) {
+          mbar_wait(&b_full[br.stage], br.phase);
+          const int nks = min(4, (p.c_in - ch * 64) >> 4);
+          const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
+#pragma unroll
+          for (int t = 0; t < kMaxT; ++t) {
+            if (t < p.T && ((bits >> t) & 1u)) {
+              mbar_wait(&a_full[ar.stage], ar.phase);
+              fence_proxy_async_smem();
+              tc_fence_after();
+              if (lane == 0) {
+                const uint32_t d = tmem_base + (uint32_t)(h * 256 + t * acc_stride);
+                const uint64_t ad0 = desc0 | (uint64_t)(((a_base + ar.stage * kStageBytes) & 0x3FFFFu) >> 4);
+                uint32_t acc = ((fresh >> t) & 1u) ? 0u : 1u;
+                for (int ks = 0; ks < nks; ++ks) {
+                  umma_f16(d, ad0 + (uint64_t)(ks * 2), bd0 + (uint64_t)(ks * 2), p.idesc, acc);
+                  acc = 1u;
+                }
+                umma_commit(&a_empty[ar.stage]);
+              }
+              __syncwarp();
+              fresh &= ~(1u << t);
+              ar.advance(S);
+            }
+          }
+          if (lane == 0) umma_commit(&b_empty[br.stage]);
           __syncwarp();
-          ++bq;
+          br.advance(kBStages);
         }
       }
       if (lane == 0) umma_commit(&t_full[h]);
@@ -312,23 +358,23 @@ __global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_const
     }
   } else {
     // ===================== weight loader =====================
+    uint8_t *sched = sched_all + 6 * kMaxK;
     const uint32_t b_base = smem_u32(b_ring);
-    int64_t bq = 0;
-    for (int64_t g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
-      const int64_t tile0 = g * p.T;
+    Ring br;
+    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+      const int64_t tile0 = (int64_t)g * p.T;
+      fill_sched(sched, p, tile0, ntiles, lane);
       for (int k = 0; k < p.K; ++k) {
-        const int kk = p.kflip ? p.K - 1 - k : k;
-        if (!group_bits(p, tile0, ntiles, kk)) continue;
+        if (!sched[k]) continue;
         for (int ch = 0; ch < p.nchunk; ++ch) {
-          const int bs = (int)(bq & 1);
-          mbar_wait(&b_empty[bs], ((uint32_t)(bq >> 1) & 1u) ^ 1u);
+          mbar_wait(&b_empty[br.stage], br.phase ^ 1u);
           if (lane == 0) {
             const uint8_t *src = (const uint8_t *)p.bpack + (((size_t)sp * p.K + k) * p.nchunk + ch) * b_bytes;
-            mbar_arrive_expect_tx(&b_full[bs], b_bytes);
-            bulk_g2s(b_base + (uint32_t)bs * b_bytes, src, b_bytes, &b_full[bs]);
+            mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
+            bulk_g2s(b_base + br.stage * b_bytes, src, b_bytes, &b_full[br.stage]);
           }
           __syncwarp();
-          ++bq;
+          br.advance(kBStages);
         }
       }
     }
@@ -336,7 +382,7 @@ __global__ void __launch_bounds__(kNumThreadsTC, 1) k_conv_tc(const __grid_const
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == 9) {
     tc_fence_after();
     tmem_dealloc_512(tmem_base);
   }
@@ -354,7 +400,7 @@ static inline size_t align256s(size_t b) { return (b + 255) & ~(size_t)255; }
 
 static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPlan &pl) {
   if (dtype != MK_BF16 && dtype != MK_F16) return false;
-  if (c_in < 16 || c_in % 16 || c_out < 16 || c_out % 16 || K < 1 || K > 128 || n_out < 1) return false;
+  if (c_in < 16 || c_in % 16 || c_out < 16 || c_out % 16 || K < 1 || K > kMaxK || n_out < 1) return false;
   int nsplit = (c_out + 255) / 256;
   while (c_out % (16 * nsplit)) ++nsplit;
   pl.nsplit = nsplit;
@@ -364,7 +410,8 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   pl.T = std::min(kMaxT, 256 / acc_stride);
   pl.W = (K + 31) / 32;
   const size_t b_bytes = (size_t)pl.NT * 128;
-  const size_t fixed = 1024 /*align slack*/ + 2 * b_bytes + 512 /*barriers*/;
+  const size_t fixed = 1024 /*align slack*/ + kBStages * b_bytes + kIdxSlots * kTileM * 4 + 7 * kMaxK +
+                       1024 /*barriers*/;
   const size_t budget = 227 * 1024;
   int S = (int)((budget - fixed) / kStageBytes);
   S = std::min(S, 12);
@@ -398,8 +445,8 @@ int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint
 
 template <typename T>
 static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const void *w, int transpose_w, int kflip,
-                             const int32_t *nbr, const uint32_t *tile_mask, int64_t ld, int64_t n_out, int K,
-                             int c_in, int c_out, void *y, void *workspace, cudaStream_t st) {
+                             const int32_t *nbr, const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in,
+                             int K, int c_in, int c_out, void *y, void *workspace, cudaStream_t st) {
   uint8_t *ws = (uint8_t *)workspace;
   T *bpack = (T *)ws;
   uint32_t *mask = (uint32_t *)(ws + pl.bpack_bytes);
@@ -416,19 +463,20 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
     tile_mask = mask;
   }
   ConvTCParams p;
-  p.x = x; p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y;
-  p.ld = ld; p.n_out = n_out; p.K = K; p.W = pl.W; p.kflip = kflip;
+  p.x = x;
+  p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y;
+  p.ld = ld; p.n_out = n_out; p.n_in = n_in; p.K = K; p.W = pl.W; p.kflip = kflip;
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
   p.a_stages = pl.a_stages;
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
-  p.ngroups = (ntiles + pl.T - 1) / pl.T;
+  p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
   static bool attr_set[2] = {false, false};
   if (!attr_set[fmt]) {
     MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set[fmt] = true;
   }
-  const int gx = (int)std::min<int64_t>(p.ngroups, std::max(1, num_sms() / pl.nsplit));
+  const int gx = (int)std::min<int64_t>((int64_t)p.ngroups, std::max(1, num_sms() / pl.nsplit));
   dim3 grid(gx, pl.nsplit);
   k_conv_tc<T><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
   MK_LAUNCH_CHECK();
@@ -436,18 +484,18 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
 }
 
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
-                const uint32_t *tile_mask, int64_t ld, int64_t n_out, int K, int c_in, int c_out, void *y,
-                void *workspace, cudaStream_t st) {
+                const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                void *y, void *workspace, cudaStream_t st) {
   TCPlan pl;
   if (!make_plan(dtype, n_out, K, c_in, c_out, pl)) {
     set_error("conv_fwd_tc: shape not eligible");
     return MK_EUNSUPPORTED;
   }
   if (dtype == MK_BF16)
-    return conv_fwd_tc_typed<__nv_bfloat16>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, K, c_in,
-                                            c_out, y, workspace, st);
-  return conv_fwd_tc_typed<__half>(pl, 0, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, K, c_in, c_out, y,
-                                   workspace, st);
+    return conv_fwd_tc_typed<__nv_bfloat16>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K,
+                                            c_in, c_out, y, workspace, st);
+  return conv_fwd_tc_typed<__half>(pl, 0, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, c_in, c_out,
+                                   y, workspace, st);
 }
 
 // weight gradient on tensor cores: conv_wgrad_tc.cu

@@ -68,6 +68,32 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// ---- TMA (cp.async.bulk.tensor) -------------------------------------------------
+// tile::gather4: four rows (row indices r.x..r.w of dimension 1) x one box of
+// columns starting at `col`, written as 4 consecutive box rows at dst with the
+// tensor map's swizzle; out-of-range rows / columns are zero-filled.  Completion
+// is counted on `bar` as the full box bytes.
+__device__ __forceinline__ void tma_gather4(uint32_t dst_smem, const void *tmap, int32_t col, int4 r,
+                                            uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes.cta_group::1 "
+      "[%0], [%1, {%2, %3, %4, %5, %6}], [%7];" ::"r"(dst_smem),
+      "l"(tmap), "r"(col), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w), "r"(smem_u32(bar))
+      : "memory");
+}
+// plain 2-D tiled load: box at (col, row)
+__device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const void *tmap, int32_t col, int32_t row,
+                                            uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3}], [%4];" ::"r"(dst_smem),
+      "l"(tmap), "r"(col), "r"(row), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void *tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
 // ---- tcgen05 ------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

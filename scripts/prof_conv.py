@@ -1,0 +1,89 @@
+"""North-star layer through the raw C-ABI, a few launches of each kernel — the
+command that the ncu captures under profiles/ are taken from.
+
+    python scripts/prof_conv.py [--r 271] [--cin 64] [--cout 64] [--iters 3] [--what fwd,dgrad,wgrad,kmap,insert]
+
+Prints CUDA-event times (median) per kernel so that the same command gives
+the un-profiled numbers.  No oracle involved (inputs are synthetic)."""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import abi  # noqa: E402
+
+
+def sphere(R, seed=0):
+    rng = np.random.default_rng(seed)
+    v = rng.normal(size=(40 * R * R, 3))
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    c = np.unique(np.floor(v * R + R + 1).astype(np.int32), axis=0)
+    return np.concatenate([np.zeros((len(c), 1), np.int32), c], 1)
+
+
+def offsets3():
+    r = np.arange(-1, 2)
+    # first spatial axis fastest
+    return np.array([[x, y, z] for z in r for y in r for x in r], np.int32)
+
+
+def timed(fn, iters):
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts)), out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--r", type=int, default=271)
+    ap.add_argument("--cin", type=int, default=64)
+    ap.add_argument("--cout", type=int, default=64)
+    ap.add_argument("--iters", type=int, default=3)
+    ap.add_argument("--what", default="insert,kmap,fwd,dgrad,wgrad")
+    ap.add_argument("--dtype", default="bf16")
+    ap.add_argument("--shuffle", type=int, default=0, help="1: random row order instead of sorted")
+    args = ap.parse_args()
+    what = set(args.what.split(","))
+    dt = {"bf16": torch.bfloat16, "f16": torch.float16, "f32": torch.float32}[args.dtype]
+    c = sphere(args.r)
+    if args.shuffle:
+        c = c[np.random.default_rng(1).permutation(len(c))]
+    n = len(c)
+    offs = offsets3()
+    t_ins, tin = timed(lambda: abi.insert(c), args.iters if "insert" in what else 1)
+    t_km, (nbr, ld, counts) = timed(lambda: abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs),
+                                    args.iters if "kmap" in what else 1)
+    P = int(counts.sum())
+    print(f"n={n} P={P} P/n={P / n:.2f} insert(+h2d/d2h)={t_ins:.3f} ms kmap(+alloc)={t_km:.3f} ms", flush=True)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, args.cin, generator=g).to(dt).cuda()
+    dy = torch.randn(n, args.cout, generator=g).to(dt).cuda()
+    w = (torch.randn(27, args.cin, args.cout, generator=g) / np.sqrt(27 * args.cin)).to(dt).cuda()
+    mask = abi.tile_mask(nbr, n, ld, 27)
+    fl = 2.0 * P * args.cin * args.cout
+    if "fwd" in what:
+        t, _ = timed(lambda: abi.conv_fwd(x, w, nbr, ld, n, mask=mask), args.iters)
+        print(f"fwd   {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  path={abi.last_path()}", flush=True)
+    if "dgrad" in what:
+        t, _ = timed(lambda: abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1, c_out=args.cin, mask=mask),
+                     args.iters)
+        print(f"dgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  path={abi.last_path()}", flush=True)
+    if "wgrad" in what:
+        t, _ = timed(lambda: abi.conv_wgrad(x, dy, nbr, ld, n, 27, mask=mask), args.iters)
+        print(f"wgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  path={abi.last_path()}", flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -95,8 +95,8 @@ def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None, mask=None
     y = torch.empty((n_out, c_out), dtype=x.dtype, device="cuda")
     ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
                      device="cuda")
-    _lib.check(lib.mk_conv_fwd(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, K, c_in, c_out,
-                               P(y), P(ws), S()))
+    _lib.check(lib.mk_conv_fwd(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0], K, c_in,
+                               c_out, P(y), P(ws), S()))
     return y
 
 
@@ -106,7 +106,8 @@ def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None):
     dw = torch.empty((K, c_in, c_out), dtype=x.dtype, device="cuda")
     ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
                      device="cuda")
-    _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), P(mask), ld, n_out, K, c_in, c_out, P(dw), P(ws), S()))
+    _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), P(mask), ld, n_out, x.shape[0], K, c_in, c_out, P(dw),
+                                 P(ws), S()))
     return dw
 
 

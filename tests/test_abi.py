@@ -43,7 +43,7 @@ def test_bad_arguments_return_status_not_abort(lib):
     assert b"power of two" in lib.mk_last_error()
     rc = lib.mk_kmap_build(None, 10, 7, None, 1024, None, 27, None, 128, None, None)
     assert rc == 1 and b"ncols" in lib.mk_last_error()
-    rc = lib.mk_conv_fwd(0, None, None, 0, 0, None, None, 4, 8, 27, 4, 4, None, None, None)  # ld < n_out
+    rc = lib.mk_conv_fwd(0, None, None, 0, 0, None, None, 4, 8, 8, 27, 4, 4, None, None, None)  # ld < n_out
     assert rc == 1
 
 
