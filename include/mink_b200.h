@@ -130,7 +130,9 @@ int mk_rows_scatter(const void *src, const int32_t *idx, int64_t n_idx,
  *   nbr[k * ld + o] = input row hit by output row o under kernel offset k,
  *                     or -1
  * (k-major so that a tile of consecutive output rows reads/writes
- * contiguous memory).  `offsets_host` is [K, ncols-1] in coordinate units
+ * contiguous memory).  The padding entries o in [n_out, ld) of every k are
+ * written as -1 by mk_kmap_build / mk_kmap_invert; the convolution kernels
+ * rely on every entry being -1 or a valid row.  `offsets_host` is [K, ncols-1] in coordinate units
  * (already multiplied by dilation * tensor_stride).
  * ---------------------------------------------------------------------- */
 int mk_kmap_build(const int32_t *out_coords, int64_t n_out, int ncols,

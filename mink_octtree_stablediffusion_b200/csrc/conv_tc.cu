@@ -269,7 +269,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         Ring irt = ir;
         for (int ch = 0; ch < p.nchunk; ++ch) {
           irt = ir;
-          const bool col_ok = (ch * 64 + c16 * 8) < p.c_in;
+          const uint32_t szok = (ch * 64 + c16 * 8) < p.c_in ? 16u : 0u;
           const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
           for (int t = 0; t < p.T; ++t) {
             if (!((bits >> t) & 1u)) continue;
@@ -282,17 +282,18 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               __syncwarp();
               if (lane == 0) mbar_arrive(&i_empty[irt.stage]);
               mbar_wait(&a_empty[ar.stage], ar.phase ^ 1u);
-              const uint32_t sbase = a_base + ar.stage * kStageBytes;
-              const int64_t o0 = (tile0 + t) * kTileM + rsub * 32;
-              const int64_t lim = p.n_out - o0;     // rows of this lane's 32 that exist
+              // the 8 swizzled chunk positions of this lane inside the stage
+              const uint32_t sb = a_base + ar.stage * kStageBytes + (uint32_t)rsub * 4096u;
+              uint32_t sbx[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) sbx[j] = sb + (uint32_t)((c16 ^ j) << 4);
+              // table entries are -1 for a missing neighbour and for rows past n_out
 #pragma unroll
               for (int i = 0; i < 32; ++i) {
                 const int32_t ri = (i & 3) == 0 ? iv[i >> 2].x : (i & 3) == 1 ? iv[i >> 2].y
                                    : (i & 3) == 2 ? iv[i >> 2].z : iv[i >> 2].w;
-                const uint32_t r = (uint32_t)(rsub * 32 + i);
-                const bool ok = col_ok && (uint32_t)ri < (uint32_t)p.n_in && i < lim;
-                const uint32_t dst = sbase + r * 128u + (uint32_t)((c16 ^ (i & 7)) << 4);
-                cp_async16(dst, ok ? (const void *)(xb + (size_t)ri * row_bytes) : p.x, ok ? 16u : 0u);
+                cp_async16(sbx[i & 7] + (uint32_t)i * 128u, xb + (size_t)(uint32_t)max(ri, 0) * row_bytes,
+                           ri >= 0 ? szok : 0u);
               }
               cp_async_arrive_noinc(&a_full[ar.stage]);
             }
@@ -333,7 +334,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               mbar_wait(&a_full[ar.stage], ar.phase);
               fence_proxy_async_smem();
               tc_fence_after();
-              if (lane == 0) {
+              if (elect_one()) {
                 const uint32_t d = tmem_base + (uint32_t)(h * 256 + t * acc_stride);
                 const uint64_t ad0 = desc0 | (uint64_t)(((a_base + ar.stage * kStageBytes) & 0x3FFFFu) >> 4);
                 uint32_t acc = ((fresh >> t) & 1u) ? 0u : 1u;
@@ -348,12 +349,12 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               ar.advance(S);
             }
           }
-          if (lane == 0) umma_commit(&b_empty[br.stage]);
+          if (elect_one()) umma_commit(&b_empty[br.stage]);
           __syncwarp();
           br.advance(kBStages);
         }
       }
-      if (lane == 0) umma_commit(&t_full[h]);
+      if (elect_one()) umma_commit(&t_full[h]);
       __syncwarp();
     }
   } else {

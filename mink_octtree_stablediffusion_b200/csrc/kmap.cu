@@ -81,7 +81,7 @@ k_kmap_build(const int32_t *__restrict__ out_coords, int64_t n_out, int ncols,
           sl = __ldg(reinterpret_cast<const uint4 *>(table + hh));
         }
       }
-      if (live) nbr[(int64_t)k * ld + o] = r;
+      if (o < ld) nbr[(int64_t)k * ld + o] = r;   // padding rows [n_out, ld) read as missing
       if (do_count) {
         const unsigned bal = __ballot_sync(0xffffffffu, r >= 0);
         if ((threadIdx.x & 31) == 0 && bal) atomicAdd(&s_cnt[k], __popc(bal));
@@ -206,7 +206,7 @@ int mk_kmap_build(const int32_t *out_coords, int64_t n_out, int ncols,
   MK_CHECK_ARG(out_coords && in_table && nbr && offsets_host, "null pointer");
   KOffsets offs;
   memcpy(offs.v, offsets_host, sizeof(int32_t) * K * (ncols - 1));
-  const unsigned blocks = (unsigned)ceil_div(n_out, kBuildThreads);
+  const unsigned blocks = (unsigned)ceil_div(ld, kBuildThreads);
   const size_t smem = counts_dev ? sizeof(int) * K : 0;
   const uint32_t mask = (uint32_t)(in_capacity - 1);
   if (K % 9 == 0)
