@@ -1,12 +1,435 @@
-// Tensor-core weight gradient (placeholder until the tcgen05 kernel lands):
-// reports "not eligible" so mk_conv_wgrad uses the SIMT split-row kernel.
+// Tensor-core (tcgen05 / TMEM) weight gradient of the sparse convolution.
+//
+// Replaces the dB part of matmul2<T,uint,TILE> behind ConvolutionBackwardGPU
+// (pybind/extern.hpp:100-114), which accumulates with atomicAdd;
+// here the result is deterministic.
+//
+//   dW[k][ci][co] = sum_o  x[nbr[k,o], ci] * dy[o, co]
+//
+// As an MMA: D[M x N] += A[M x 16] B[16 x N] with the 16 reduced "k" being
+// output rows o.  A = gathered x rows, B = dy rows; both sit in shared memory
+// exactly as they sit in global memory (row = voxel, 128 contiguous bytes = 64
+// channels, 128B swizzle), which for UMMA is the MN-major canonical layout.
+//
+// Work decomposition
+//   panel  = (offset k, 64-channel chunk of c_in): one gathered [128 x 64] tile
+//   pair   = two consecutive panels = the M=128 rows of one accumulator
+//   unit   = (pair, n-split): a [128 x NB] fp32 accumulator = NB TMEM columns
+// A CTA owns up to U = 512/NB units for its whole life (accumulators never
+// leave TMEM until the end) and walks the 128-row tiles xs, xs+X, ...; for each
+// tile it loads the dy tile once (TMA) and, per pair, gathers the two panels
+// (LDGSTS, zero-fill for missing neighbours).  Pairs whose offsets have no
+// neighbour in the tile are skipped via the kernel map's tile mask.  At the end
+// each CTA writes its fp32 partial to the workspace and a second kernel sums
+// the X partials in a fixed order.
+//
+// CTA roles (224 threads, 1 CTA / SM):
+//   warps 0-3  gather producers, then the epilogue (TMEM -> fp32 partial)
+//   warp  4    neighbour-index prefetch (bulk copies into a smem ring)
+//   warp  5    MMA issuer
+//   warp  6    dy tile loader (TMA)
+#include <algorithm>
+
 #include "common.cuh"
+#include "sm100.cuh"
+#include "tmap.cuh"
+
 namespace mk {
-bool conv_wgrad_tc_eligible(int, int64_t, int, int, int) { return false; }
-int64_t conv_wgrad_tc_workspace(int64_t, int, int, int) { return 0; }
-int conv_wgrad_tc(int, const void *, const void *, const int32_t *, const uint32_t *, int64_t, int64_t, int64_t, int, int,
-                  int, void *, void *, cudaStream_t) {
-  set_error("conv_wgrad_tc: not built");
-  return MK_EUNSUPPORTED;
+using namespace sm100;
+
+namespace wg {
+constexpr int kTileM = 128;
+constexpr int kPanelBytes = kTileM * 128;   // [128 rows x 64 ch] 16-bit
+constexpr int kStageBytes = 2 * kPanelBytes;
+constexpr int kThreads = 224;
+constexpr int kGatherWarps = 4;
+constexpr int kIdxSlots = 32;
+constexpr int kMaxUnits = 16;
+
+struct Params {
+  const void *x;          // [n_in, c_in]
+  const int32_t *nbr;     // [K, ld]
+  const uint32_t *mask;   // [ntiles, W]
+  float *partial;         // [X][K][c_in][c_out]
+  int64_t ld, n_out, n_in;
+  int K, W, c_in, c_out;
+  int pa;                 // 64-channel panels per offset
+  int npairs, ppg;        // pairs in total / per CTA group
+  int G;                  // pair groups (blockIdx.y = ns * G + g)
+  int NB, nbpad, pb;      // accumulator columns, padded stride, dy panels per tile
+  int a_stages, b_bufs;
+  int ntiles, X;
+  uint32_t idesc;
+};
+
+struct Ring {
+  uint32_t stage = 0, phase = 0;
+  __device__ __forceinline__ void advance(uint32_t n) {
+    if (++stage == n) { stage = 0; phase ^= 1u; }
+  }
+};
+
+// bit k of a tile's mask words (W <= 4)
+__device__ __forceinline__ uint32_t mask_bit(const uint32_t (&w)[4], int k) {
+  const uint32_t word = k < 32 ? w[0] : k < 64 ? w[1] : k < 96 ? w[2] : w[3];
+  return (word >> (k & 31)) & 1u;
 }
+
+// per-tile view of this CTA's pairs: bit u of `pairs` = pair j0+u has work;
+// bits 2u / 2u+1 of `panels` = its first / second panel is real and non-empty
+struct TileSched { uint32_t pairs, panels; };
+
+__device__ __forceinline__ TileSched tile_sched(const Params &p, int tile, int j0, int npair_cta) {
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
+  for (int i = 0; i < p.W; ++i) w[i] = __ldg(p.mask + (int64_t)tile * p.W + i);
+  TileSched s{0u, 0u};
+  for (int u = 0; u < npair_cta; ++u) {
+    const int q0 = 2 * (j0 + u);
+    const int k0 = q0 / p.pa, k1 = (q0 + 1) / p.pa;
+    const uint32_t b0 = mask_bit(w, k0);
+    const uint32_t b1 = k1 < p.K ? mask_bit(w, k1) : 0u;
+    s.pairs |= (b0 | b1) << u;
+    s.panels |= (b0 << (2 * u)) | (b1 << (2 * u + 1));
+  }
+  return s;
+}
+}  // namespace wg
+
+__global__ void __launch_bounds__(wg::kThreads, 1)
+k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CUtensorMap tmap_dy) {
+  using namespace wg;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t S = (uint32_t)p.a_stages, NBUF = (uint32_t)p.b_bufs;
+  const uint32_t b_bytes = (uint32_t)p.pb * kPanelBytes;
+  uint8_t *a_ring = smem;
+  uint8_t *b_ring = a_ring + (size_t)S * kStageBytes;
+  int32_t *idx_ring = (int32_t *)(b_ring + (size_t)NBUF * b_bytes);
+  uint64_t *bars = (uint64_t *)(idx_ring + kIdxSlots * kTileM);
+  uint64_t *a_full = bars, *a_empty = a_full + S;
+  uint64_t *b_full = a_empty + S, *b_empty = b_full + NBUF;
+  uint64_t *i_full = b_empty + NBUF, *i_empty = i_full + kIdxSlots;
+  uint64_t *done = i_empty + kIdxSlots;
+  uint32_t *tmem_slot = (uint32_t *)(done + 1);
+  uint32_t *inited_slot = tmem_slot + 1;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.y % p.G, ns = blockIdx.y / p.G;
+  const int j0 = g * p.ppg;
+  const int npair_cta = min(p.ppg, p.npairs - j0);
+  const int xs = blockIdx.x;
+
+  if (threadIdx.x == 0) {
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 64); mbar_init(&a_empty[s], 1); }
+    for (uint32_t s = 0; s < NBUF; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], 1); }
+    mbar_init(done, 1);
+    *inited_slot = 0u;
+    fence_barrier_init();
+  }
+  if (warp == 6 && lane == 0) tma_prefetch_desc(&tmap_dy);
+  if (warp == 5) tmem_alloc_512(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < kGatherWarps) {
+    // ===================== gather producers =====================
+    // one work item = one panel; items are dealt round-robin to the four warps.
+    // lane = (rsub, c16): instruction i moves 16-byte chunk c16 of panel rows
+    // rsub*32 + i (four 128-byte feature rows per warp instruction)
+    const uint32_t a_base = smem_u32(a_ring);
+    const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
+    const int c16 = lane & 7, rsub = lane >> 3;
+    Ring ir, ar;
+    uint32_t e = 0;
+    for (int tile = xs; tile < p.ntiles; tile += p.X) {
+      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      for (int u = 0; u < npair_cta; ++u) {
+        if (!((ts.pairs >> u) & 1u)) continue;
+        for (int hf = 0; hf < 2; ++hf, ++e) {
+          const bool real = (ts.panels >> (2 * u + hf)) & 1u;
+          const bool mine = (e & (kGatherWarps - 1)) == (uint32_t)warp;
+          if (mine) {
+            const int q = 2 * (j0 + u) + hf;
+            const int pi = q % p.pa;
+            const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
+            const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
+            int4 iv[8];
+            if (real) {
+              mbar_wait(&i_full[ir.stage], ir.phase);
+              const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + ir.stage * kTileM + rsub * 32);
+#pragma unroll
+              for (int qq = 0; qq < 8; ++qq) iv[qq] = ip[qq];
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
+            } else {
+#pragma unroll
+              for (int qq = 0; qq < 8; ++qq) iv[qq] = make_int4(-1, -1, -1, -1);
+            }
+            mbar_wait(&a_empty[ar.stage], ar.phase ^ 1u);
+            const uint32_t sb = a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)rsub * 4096u;
+            uint32_t sbx[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sbx[j] = sb + (uint32_t)((c16 ^ j) << 4);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int32_t ri = (i & 3) == 0 ? iv[i >> 2].x : (i & 3) == 1 ? iv[i >> 2].y
+                                 : (i & 3) == 2 ? iv[i >> 2].z : iv[i >> 2].w;
+              cp_async16(sbx[i & 7] + (uint32_t)i * 128u, xb + (size_t)(uint32_t)max(ri, 0) * row_bytes,
+                         ri >= 0 ? szok : 0u);
+            }
+            cp_async_arrive_noinc(&a_full[ar.stage]);
+          }
+          if (real) ir.advance(kIdxSlots);
+        }
+        ar.advance(S);
+      }
+    }
+    // ===================== epilogue: TMEM -> fp32 partial =====================
+    mbar_wait(done, 0u);
+    tc_fence_after();
+    const uint32_t inited = *(volatile uint32_t *)inited_slot;
+    float *part = p.partial + (size_t)xs * p.K * p.c_in * p.c_out;
+    for (int u = 0; u < npair_cta; ++u) {
+      const int r = warp * 32 + lane;                 // accumulator row = TMEM lane
+      const int q = 2 * (j0 + u) + (r >> 6);
+      const int k = q / p.pa, ci = (q % p.pa) * 64 + (r & 63);
+      const bool row_ok = k < p.K && ci < p.c_in;
+      float *dst = part + ((size_t)k * p.c_in + ci) * p.c_out + (size_t)ns * p.NB;
+      const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(u * p.nbpad);
+      for (int c0 = 0; c0 < p.NB; c0 += 16) {
+        uint32_t v[16];
+        if ((inited >> u) & 1u) {
+          tmem_ld16(tbase + (uint32_t)c0, v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = 0u;
+        }
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            *reinterpret_cast<uint4 *>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+      }
+    }
+    tc_fence_before();
+  } else if (warp == 4) {
+    // ===================== neighbour-index prefetch =====================
+    const uint32_t i_base = smem_u32(idx_ring);
+    Ring ir;
+    for (int tile = xs; tile < p.ntiles; tile += p.X) {
+      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      for (int u = 0; u < npair_cta; ++u) {
+        for (int hf = 0; hf < 2; ++hf) {
+          if (!((ts.panels >> (2 * u + hf)) & 1u)) continue;
+          const int k = (2 * (j0 + u) + hf) / p.pa;
+          mbar_wait(&i_empty[ir.stage], ir.phase ^ 1u);
+          if (lane == 0) {
+            const int32_t *src = p.nbr + (int64_t)k * p.ld + (int64_t)tile * kTileM;
+            mbar_arrive_expect_tx(&i_full[ir.stage], kTileM * 4);
+            bulk_g2s(i_base + ir.stage * (kTileM * 4), src, kTileM * 4, &i_full[ir.stage]);
+          }
+          __syncwarp();
+          ir.advance(kIdxSlots);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer =====================
+    const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
+    // MN-major SW128 operands: LBO = distance between 64-channel panels,
+    // SBO = 1024 B between 8-row groups; 16 rows (one MMA) = 2048 B
+    const uint64_t desc0 = smem_desc_sw128(0, kPanelBytes, 1024);
+    Ring ar, br;
+    uint32_t inited = 0;
+    for (int tile = xs; tile < p.ntiles; tile += p.X) {
+      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      if (!ts.pairs) continue;
+      mbar_wait(&b_full[br.stage], br.phase);
+      const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
+      for (int u = 0; u < npair_cta; ++u) {
+        if (!((ts.pairs >> u) & 1u)) continue;
+        mbar_wait(&a_full[ar.stage], ar.phase);
+        fence_proxy_async_smem();
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d = tmem_base + (uint32_t)(u * p.nbpad);
+          const uint64_t ad0 = desc0 | (uint64_t)(((a_base + ar.stage * kStageBytes) & 0x3FFFFu) >> 4);
+          uint32_t acc = (inited >> u) & 1u;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            umma_f16(d, ad0 + (uint64_t)(ks * 128), bd0 + (uint64_t)(ks * 128), p.idesc, acc);
+            acc = 1u;
+          }
+          umma_commit(&a_empty[ar.stage]);
+        }
+        __syncwarp();
+        inited |= 1u << u;
+        ar.advance(S);
+      }
+      if (elect_one()) umma_commit(&b_empty[br.stage]);
+      __syncwarp();
+      br.advance(NBUF);
+    }
+    if (lane == 0) { *inited_slot = inited; __threadfence_block(); }
+    __syncwarp();
+    if (elect_one()) {
+      if (inited) umma_commit(done);
+      else mbar_arrive(done);
+    }
+    __syncwarp();
+  } else {
+    // ===================== dy tile loader (TMA) =====================
+    const uint32_t b_base = smem_u32(b_ring);
+    Ring br;
+    for (int tile = xs; tile < p.ntiles; tile += p.X) {
+      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      if (!ts.pairs) continue;
+      mbar_wait(&b_empty[br.stage], br.phase ^ 1u);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
+        for (int pn = 0; pn < p.pb; ++pn)
+          tma_load_2d(b_base + br.stage * b_bytes + (uint32_t)pn * kPanelBytes, &tmap_dy, ns * p.NB + pn * 64,
+                      tile * kTileM, &b_full[br.stage]);
+      }
+      __syncwarp();
+      br.advance(NBUF);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc_512(tmem_base);
+  }
+}
+
+// dw[e] = sum over the X partials, fixed order
+template <typename T>
+__global__ void k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t n, T *__restrict__ dw) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int s = 0; s < X; ++s) {
+    const float4 v = __ldg(reinterpret_cast<const float4 *>(partial + (size_t)s * n + i));
+    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  }
+  dw[i] = from_acc<T, float>(acc.x);
+  dw[i + 1] = from_acc<T, float>(acc.y);
+  dw[i + 2] = from_acc<T, float>(acc.z);
+  dw[i + 3] = from_acc<T, float>(acc.w);
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+namespace {
+struct WPlan {
+  int pa, npairs, nsplit, NB, nbpad, pb, U, G, ppg, a_stages, b_bufs, ntiles, X, W;
+  size_t smem, partial_bytes, mask_bytes;
+};
+
+inline size_t align256w(size_t b) { return (b + 255) & ~(size_t)255; }
+
+bool make_wplan(int dtype, int64_t n_out, int K, int c_in, int c_out, WPlan &pl) {
+  using namespace wg;
+  if (dtype != MK_BF16 && dtype != MK_F16) return false;
+  if (c_in < 16 || c_in % 16 || c_out < 16 || c_out % 16 || K < 1 || K > 128 || n_out < 1) return false;
+  if (n_out > (int64_t)kTileM * 0x7fffff00) return false;
+  pl.pa = (c_in + 63) / 64;
+  pl.npairs = (K * pl.pa + 1) / 2;
+  int nsplit = (c_out + 255) / 256;
+  while (c_out % (16 * nsplit)) ++nsplit;
+  pl.nsplit = nsplit;
+  pl.NB = c_out / nsplit;
+  pl.nbpad = (pl.NB + 31) & ~31;
+  pl.pb = (pl.NB + 63) / 64;
+  pl.U = std::min(kMaxUnits, 512 / pl.nbpad);
+  pl.G = (pl.npairs + pl.U - 1) / pl.U;
+  pl.ppg = (pl.npairs + pl.G - 1) / pl.G;
+  pl.G = (pl.npairs + pl.ppg - 1) / pl.ppg;
+  pl.W = (K + 31) / 32;
+  pl.ntiles = (int)((n_out + kTileM - 1) / kTileM);
+  const int ctas_y = pl.G * nsplit;
+  pl.X = std::max(1, std::min(pl.ntiles, num_sms() / ctas_y));
+  const size_t b_tile = (size_t)pl.pb * kPanelBytes;
+  const size_t fixed = 1024 + (size_t)kIdxSlots * kTileM * 4 + 1024;
+  const size_t budget = 227 * 1024;
+  pl.b_bufs = 2;
+  if (fixed + 2 * b_tile + 2 * (size_t)kStageBytes > budget) pl.b_bufs = 1;
+  if (fixed + pl.b_bufs * b_tile + 2 * (size_t)kStageBytes > budget) return false;
+  pl.a_stages = (int)std::min<size_t>(6, (budget - fixed - pl.b_bufs * b_tile) / kStageBytes);
+  pl.smem = fixed + pl.b_bufs * b_tile + (size_t)pl.a_stages * kStageBytes;
+  pl.partial_bytes = align256w((size_t)pl.X * K * c_in * c_out * 4);
+  pl.mask_bytes = align256w((size_t)pl.ntiles * pl.W * 4);
+  return true;
+}
+}  // namespace
+
+int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint32_t *mask, cudaStream_t st);
+
+bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) {
+  WPlan pl;
+  return make_wplan(dtype, n_out, K, c_in, c_out, pl);
+}
+
+int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
+  WPlan pl;
+  if (!make_wplan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return 0;
+  return (int64_t)(pl.partial_bytes + pl.mask_bytes + 256);
+}
+
+int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, const uint32_t *tile_mask,
+                  int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out, void *dw, void *workspace,
+                  cudaStream_t st) {
+  using namespace wg;
+  WPlan pl;
+  if (!make_wplan(dtype, n_out, K, c_in, c_out, pl)) {
+    set_error("conv_wgrad_tc: shape not eligible");
+    return MK_EUNSUPPORTED;
+  }
+  uint8_t *ws = (uint8_t *)workspace;
+  float *partial = (float *)ws;
+  if (tile_mask == nullptr) {
+    uint32_t *mask = (uint32_t *)(ws + pl.partial_bytes);
+    int rc = tile_mask_launch(nbr, n_out, ld, K, mask, st);
+    if (rc) return rc;
+    tile_mask = mask;
+  }
+  CUtensorMap tmap_dy;
+  {
+    int rc = make_tmap_rows16(&tmap_dy, dtype, dy, n_out, c_out, 64, kTileM);
+    if (rc) return rc;
+  }
+  Params p;
+  p.x = x; p.nbr = nbr; p.mask = tile_mask; p.partial = partial;
+  p.ld = ld; p.n_out = n_out; p.n_in = n_in;
+  p.K = K; p.W = pl.W; p.c_in = c_in; p.c_out = c_out;
+  p.pa = pl.pa; p.npairs = pl.npairs; p.ppg = pl.ppg; p.G = pl.G;
+  p.NB = pl.NB; p.nbpad = pl.nbpad; p.pb = pl.pb;
+  p.a_stages = pl.a_stages; p.b_bufs = pl.b_bufs;
+  p.ntiles = pl.ntiles; p.X = pl.X;
+  p.idesc = idesc_f16(dtype == MK_BF16 ? 1 : 0, kTileM, pl.NB, 1, 1);
+  static bool attr_set = false;
+  if (!attr_set) {
+    MK_CUDA(cudaFuncSetAttribute(k_conv_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  dim3 grid(pl.X, pl.G * pl.nsplit);
+  k_conv_wgrad_tc<<<grid, kThreads, pl.smem, st>>>(p, tmap_dy);
+  MK_LAUNCH_CHECK();
+  const int64_t n_w = (int64_t)K * c_in * c_out;
+  const unsigned blocks = (unsigned)ceil_div(n_w / 4, 256);
+  if (dtype == MK_BF16)
+    k_wgrad_reduce<__nv_bfloat16><<<blocks, 256, 0, st>>>(partial, pl.X, n_w, (__nv_bfloat16 *)dw);
+  else
+    k_wgrad_reduce<__half><<<blocks, 256, 0, st>>>(partial, pl.X, n_w, (__half *)dw);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
 }  // namespace mk
