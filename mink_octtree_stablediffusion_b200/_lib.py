@@ -8,6 +8,7 @@ missing or a call fails, a RuntimeError is raised.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
@@ -66,6 +67,15 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
+    override = os.environ.get("MK_B200_LIB")      # developer aid: A/B a differently built library
+    if override:
+        lib = C.CDLL(override)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+        return lib
     if not LIB_PATH.exists():
         if not build_if_missing:
             raise RuntimeError(f"{LIB_PATH} is missing; run `python -m mink_octtree_stablediffusion_b200.build`")

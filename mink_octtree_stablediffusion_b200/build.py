@@ -27,7 +27,7 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",
     "-Xptxas", "-v",
-]
+] + os.environ.get("MK_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

@@ -7,22 +7,27 @@
 //
 //   y[o, n0:n0+NT] = sum_k  x[nbr[kk(k), o], :] @ B_k          (fp32 accumulate)
 //
-// CTA roles (352 threads, 1 CTA / SM, all 512 TMEM columns):
-//   warps 0-3  epilogue : tcgen05.ld accumulators -> bf16/f16 -> global
-//   warp  4    indices  : one lane bulk-copies the 128 neighbour-table entries
-//                         of every (tile, offset) into a ring in shared memory
-//   warps 5-8  gather   : LDGSTS 16-byte chunks of the neighbour rows into a
-//                         ring of 128-row x 128-byte A stages (128B swizzle),
-//                         missing neighbours zero-filled; stages are dealt
-//                         round-robin to the four warps
-//   warp  9    MMA      : one lane issues tcgen05.mma (M=128, N=NT, K=16)
-//   warp  10   weights  : one lane bulk-copies the pre-swizzled B image of each
-//                         (offset, channel chunk) into a ring
+// CTA roles (736 threads, 1 CTA / SM, all 512 TMEM columns):
+//   warps 0-3   epilogue : tcgen05.ld accumulators -> bf16/f16 -> global
+//   warp  4     indices  : one lane bulk-copies, per offset, the T*128 neighbour-
+//                          table entries of the group into a ring in shared memory
+//   warp  5     weights  : one lane bulk-copies the pre-swizzled B image of each
+//                          (offset, channel chunk) into a ring
+//   warp  6     MMA      : driven by tickets; one elected lane issues tcgen05.mma
+//                          (M=128, N=NT, K=16) from uniform registers
+//   warps 7-22  gather   : four teams of four warps; LDGSTS 16-byte chunks of the
+//                          neighbour rows into the A stage (128B swizzle), missing
+//                          neighbours zero-filled
 // A CTA owns "groups" of T 128-row output tiles whose accumulators live side by
 // side in one half of TMEM; the two halves ping-pong so the epilogue of one
-// group overlaps the main loop of the next.  Which (tile, offset) pairs have
-// any neighbour at all is known up front from the kernel map's tile mask, so
-// every role walks the same static schedule and empty pairs are skipped.
+// group overlaps the main loop of the next.  One A stage holds the T gathered
+// tiles of the group under one (offset, channel chunk) - a coarse stage keeps the
+// number of barrier hand-offs per MMA low, which is what bounds this kernel.
+// Which (tile, offset) pairs have any neighbour at all is known up front from
+// the kernel map's tile mask, so every role walks the same static schedule and
+// empty pairs are skipped.  The gather teams, which walk the schedule anyway,
+// hand the MMA warp a "ticket" per stage (tiles present, accumulate flags, group
+// begin / end) so that the serial MMA warp does no bookkeeping.
 #include <algorithm>
 #include <cstdlib>
 
@@ -34,12 +39,18 @@ namespace mk {
 using namespace sm100;
 
 constexpr int kTileM = 128;
-constexpr int kStageBytes = kTileM * 128;  // one A stage: 128 rows x 64 16-bit channels
-constexpr int kNumThreadsTC = 352;
-constexpr int kGatherWarps = 4;
+constexpr int kTileBytes = kTileM * 128;   // one gathered tile: 128 rows x 64 16-bit channels
+// one A stage = the T tiles of a group under one (offset, channel chunk): T * kTileBytes
+constexpr int kGatherTeams = 4;              // stages in flight on the producer side
+constexpr int kGatherWarps = 4 * kGatherTeams;   // 4 warps (32 rows each) per stage
+constexpr int kMmaWarps = 1;   // stages must be released in order: the parity waits of the producer
+                               // teams are only alias-free when consumption is in order
+constexpr int kWarpIdx = 4, kWarpWeights = 5, kWarpMma0 = 6, kWarpGather0 = kWarpMma0 + kMmaWarps;
+constexpr int kNumThreadsTC = 32 * (kWarpGather0 + kGatherWarps);
+constexpr int kSchedCopies = 2 + kGatherWarps;
 constexpr int kMaxT = 4;                   // tiles per group (256 TMEM columns / NT)
-constexpr int kIdxSlots = 32;              // ring of 512-byte neighbour-index rows
-constexpr int kBStages = 4;                // weight-image ring
+constexpr int kIdxSlots = 4;               // ring of neighbour-index rows: one slot = the T*128 entries of a group under one offset
+constexpr int kBStages = 2;                // weight-image ring
 constexpr int kMaxK = 128;
 
 struct ConvTCParams {
@@ -61,6 +72,10 @@ struct Ring {
   uint32_t stage = 0, phase = 0;
   __device__ __forceinline__ void advance(uint32_t n) {
     if (++stage == n) { stage = 0; phase ^= 1u; }
+  }
+  __device__ __forceinline__ void skip(uint32_t by, uint32_t n) {
+    stage += by;
+    while (stage >= n) { stage -= n; phase ^= 1u; }
   }
 };
 
@@ -126,9 +141,10 @@ template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) 
 // Per-role copy of a group's schedule: sched[k] = T-bit mask of the group's
 // tiles that have any neighbour under the table offset used by weight k.
 // Called by a whole (converged) warp.
-__device__ __forceinline__ void fill_sched(uint8_t *sched, const ConvTCParams &p, int64_t tile0, int64_t ntiles,
-                                           int lane) {
+__device__ __forceinline__ uint32_t fill_sched(uint8_t *sched, const ConvTCParams &p, int64_t tile0,
+                                               int64_t ntiles, int lane) {
   __syncwarp();
+  uint32_t cnt = 0;
   for (int k = lane; k < p.K; k += 32) {
     const int kk = p.kflip ? p.K - 1 - k : k;
     uint32_t bits = 0;
@@ -137,11 +153,20 @@ __device__ __forceinline__ void fill_sched(uint8_t *sched, const ConvTCParams &p
       if (tile < ntiles) bits |= ((__ldg(p.mask + tile * p.W + (kk >> 5)) >> (kk & 31)) & 1u) << t;
     }
     sched[k] = (uint8_t)bits;
+    cnt += bits ? 1u : 0u;
   }
   __syncwarp();
+  return __reduce_add_sync(0xffffffffu, cnt);   // number of offsets with any neighbour in the group
 }
 
-template <typename T>
+// Ticket: what the MMA warp has to do with one A stage (= the T gathered tiles of
+// one offset and channel chunk), written by a gather team (the teams walk the
+// schedule anyway; the MMA warp is the serial resource of the CTA and must not).
+//   bits 0-3 tiles present, bits 4-7 tiles whose accumulator already holds data,
+//   bit 8 TMEM half, bits 16-18 K steps
+constexpr uint32_t kTkGroupBegin = 1u << 12, kTkGroupEnd = 1u << 13, kTkEmptyParity = 1u << 14, kTkEnd = 1u << 15;
+
+template <typename T, bool kFull>
 __global__ void __launch_bounds__(kNumThreadsTC, 1)
 k_conv_tc(const __grid_constant__ ConvTCParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -150,10 +175,12 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   const uint32_t S = (uint32_t)p.a_stages;
   const uint32_t b_bytes = (uint32_t)p.NT * 128u;
   uint8_t *a_ring = smem;
-  uint8_t *b_ring = a_ring + (size_t)S * kStageBytes;
+  const uint32_t stage_bytes = (uint32_t)p.T * kTileBytes;
+  uint8_t *b_ring = a_ring + (size_t)S * stage_bytes;
   int32_t *idx_ring = (int32_t *)(b_ring + kBStages * b_bytes);
-  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * kTileM);   // 4 role copies x kMaxK
-  uint64_t *bars = (uint64_t *)(sched_all + 7 * kMaxK);
+  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * kMaxT * kTileM);   // per-role copies x kMaxK
+  uint32_t *tickets = (uint32_t *)(sched_all + kSchedCopies * kMaxK);   // [S]
+  uint64_t *bars = (uint64_t *)(tickets + 16);
   uint64_t *a_full = bars, *a_empty = a_full + S;
   uint64_t *b_full = a_empty + S, *b_empty = b_full + kBStages;
   uint64_t *i_full = b_empty + kBStages, *i_empty = i_full + kIdxSlots;
@@ -166,13 +193,13 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   const int acc_stride = (p.NT + 31) & ~31;
 
   if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 32); mbar_init(&a_empty[s], 1); }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u); mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)p.nchunk); }
+    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
     for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc_512(tmem_slot);
+  if (warp == kWarpMma0) tmem_alloc_512(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -180,12 +207,18 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
 
   if (warp < 4) {
     // ===================== epilogue =====================
-    uint32_t it = 0;
-    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
+    uint32_t it = 0;   // counts the groups that have any work (the others never reach the MMA thread)
+    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
       const uint32_t h = it & 1u;
       const int64_t tile0 = (int64_t)g * p.T;
-      mbar_wait(&t_full[h], (it >> 1) & 1u);
-      tc_fence_after();
+      uint32_t any = 0;
+      for (int t = 0; t < p.T; ++t)
+        if (tile0 + t < ntiles)
+          for (int wi = 0; wi < p.W; ++wi) any |= __ldg(p.mask + (tile0 + t) * p.W + wi);
+      if (any) {
+        mbar_wait_warp(&t_full[h], (it >> 1) & 1u, 3);   // outermost wait: report inner stalls first
+        tc_fence_after();
+      }
       for (int t = 0; t < p.T; ++t) {
         const int64_t tile = tile0 + t;
         if (tile >= ntiles) break;
@@ -218,14 +251,17 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&t_empty[h]);
+      if (any) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[h]);
+        ++it;
+      }
     }
-  } else if (warp == 4) {
+  } else if (warp == kWarpIdx) {
     // ===================== neighbour-index prefetch =====================
-    // one 512-byte row of the table per (offset, tile) -> idx ring; the channel
-    // chunks of a stage reuse the same indices, so the gather warp re-reads them
+    // one slot of the idx ring per offset: the T*128 table entries of the group; the
+    // channel chunks of an offset reuse the slot
     uint8_t *sched = sched_all + 0 * kMaxK;
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
@@ -236,130 +272,159 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         const uint32_t bits = sched[k];
         if (!bits) continue;
         const int kk = p.kflip ? p.K - 1 - k : k;
-        for (int t = 0; t < p.T; ++t) {
-          if (!((bits >> t) & 1u)) continue;
-          mbar_wait(&i_empty[ir.stage], ir.phase ^ 1u);
-          if (lane == 0) {
-            const int32_t *src = p.nbr + (int64_t)kk * p.ld + (tile0 + t) * kTileM;
-            mbar_arrive_expect_tx(&i_full[ir.stage], kTileM * 4);
-            bulk_g2s(i_base + ir.stage * (kTileM * 4), src, kTileM * 4, &i_full[ir.stage]);
-          }
-          __syncwarp();
-          ir.advance(kIdxSlots);
+        mbar_wait_warp(&i_empty[ir.stage], ir.phase ^ 1u);
+        if (lane == 0) {
+          // the T tiles of a group are consecutive rows of the table: one copy
+          const int64_t first = tile0 * kTileM;
+          const uint32_t bytes = (uint32_t)min((int64_t)p.T * kTileM, p.ld - first) * 4u;
+          const int32_t *src = p.nbr + (int64_t)kk * p.ld + first;
+          mbar_arrive_expect_tx(&i_full[ir.stage], bytes);
+          bulk_g2s(i_base + ir.stage * (kMaxT * kTileM * 4), src, bytes, &i_full[ir.stage]);
         }
+        __syncwarp();
+        ir.advance(kIdxSlots);
       }
     }
-  } else if (warp < 5 + kGatherWarps) {
+  } else if (warp >= kWarpGather0) {
     // ===================== gather producers (LDGSTS) =====================
-    // lane = (rsub, c16): instruction i of a stage moves 16-byte chunk c16 of tile
-    // rows rsub*32 + i, i.e. four 128-byte feature rows per warp instruction
-    const int w = warp - 5;
-    uint8_t *sched = sched_all + (1 + w) * kMaxK;
+    // Four teams of four warps.  Tile slot t of stage number n (stages are counted
+    // over the whole life of the CTA) belongs to team (n*T + t) & 3, so the stages
+    // of a team are at most 4/T < S apart, which keeps the parity waits on a_empty
+    // alias-free as long as the MMA warp releases stages in order.  Warp q of a
+    // team moves tile rows [32q, 32q+32); lane = (rsub, c16): instruction i moves
+    // 16-byte chunk c16 of rows 32q + 8*rsub + i (four 128-byte feature rows per
+    // warp instruction).  Completion is tracked by the hardware
+    // (cp.async.mbarrier.arrive.noinc); a team whose tile has no neighbour under
+    // the offset just arrives; one extra arrive publishes the ticket.
+    const int gw = warp - kWarpGather0;
+    const uint32_t team = (uint32_t)gw >> 2;
+    const int q = gw & 3;
+    uint8_t *sched = sched_all + (2 + gw) * kMaxK;
     const uint32_t a_base = smem_u32(a_ring);
     const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
     const int c16 = lane & 7, rsub = lane >> 3;
-    Ring ir, ar;
-    uint32_t e = 0;
+    const int row0 = 32 * q + 8 * rsub;            // first of this lane's 8 rows (multiple of 8)
+    const uint32_t T = (uint32_t)p.T;
+    Ring ir, ar;                                   // idx slot of the row's first tile / current A stage
+    uint32_t nst = 0;                              // stages so far
+    uint32_t it = 0;                               // groups with work so far
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
       const int64_t tile0 = (int64_t)g * p.T;
-      fill_sched(sched, p, tile0, ntiles, lane);
+      const uint32_t n_stages = fill_sched(sched, p, tile0, ntiles, lane) * (uint32_t)p.nchunk;
+      if (!n_stages) continue;
+      const uint32_t tk_group = (it & 1u) << 8 | ((((it >> 1) & 1u) ^ 1u) ? kTkEmptyParity : 0u);
+      uint32_t seen = 0, done = 0;                 // tiles already accumulated into / stages of the group so far
       for (int k = 0; k < p.K; ++k) {
         const uint32_t bits = sched[k];
         if (!bits) continue;
-        Ring irt = ir;
-        for (int ch = 0; ch < p.nchunk; ++ch) {
-          irt = ir;
-          const uint32_t szok = (ch * 64 + c16 * 8) < p.c_in ? 16u : 0u;
-          const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
-          for (int t = 0; t < p.T; ++t) {
-            if (!((bits >> t) & 1u)) continue;
-            if ((e & (kGatherWarps - 1)) == (uint32_t)w) {
-              mbar_wait(&i_full[irt.stage], irt.phase);
-              const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + irt.stage * kTileM + rsub * 32);
-              int4 iv[8];
-#pragma unroll
-              for (int q = 0; q < 8; ++q) iv[q] = ip[q];
-              __syncwarp();
-              if (lane == 0) mbar_arrive(&i_empty[irt.stage]);
-              mbar_wait(&a_empty[ar.stage], ar.phase ^ 1u);
-              // the 8 swizzled chunk positions of this lane inside the stage
-              const uint32_t sb = a_base + ar.stage * kStageBytes + (uint32_t)rsub * 4096u;
-              uint32_t sbx[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) sbx[j] = sb + (uint32_t)((c16 ^ j) << 4);
-              // table entries are -1 for a missing neighbour and for rows past n_out
-#pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                const int32_t ri = (i & 3) == 0 ? iv[i >> 2].x : (i & 3) == 1 ? iv[i >> 2].y
-                                   : (i & 3) == 2 ? iv[i >> 2].z : iv[i >> 2].w;
-                cp_async16(sbx[i & 7] + (uint32_t)i * 128u, xb + (size_t)(uint32_t)max(ri, 0) * row_bytes,
-                           ri >= 0 ? szok : 0u);
-              }
-              cp_async_arrive_noinc(&a_full[ar.stage]);
+        for (int ch = 0; ch < p.nchunk; ++ch, ++nst, ++done) {
+          bool waited = false;
+          for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
+            if (!waited) { mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u); waited = true; }
+            if (t == 0 && q == 0 && lane == 0) {
+              const uint32_t nks = kFull ? 4u : (uint32_t)min(4, (p.c_in - ch * 64) >> 4);
+              uint32_t tk = tk_group | bits | ((ch > 0 ? 0xFu : seen) << 4) | (nks << 16);
+              if (done == 0) tk |= kTkGroupBegin;
+              if (done == n_stages - 1) tk |= kTkGroupEnd;
+              tickets[ar.stage] = tk;
+              mbar_arrive(&a_full[ar.stage]);      // release: orders the ticket before the phase completes
             }
-            irt.advance(kIdxSlots);
-            ar.advance(S);
-            ++e;
+            if (!((bits >> t) & 1u)) {
+              mbar_arrive(&a_full[ar.stage]);      // nothing to gather: stand in for the cp.async arrivals
+              if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
+              continue;
+            }
+            mbar_wait_warp(&i_full[ir.stage], ir.phase);
+            const int4 *ip =
+                reinterpret_cast<const int4 *>(idx_ring + ir.stage * (kMaxT * kTileM) + t * kTileM + row0);
+            const int4 i0 = ip[0], i1 = ip[1];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
+            const uint32_t szok = (ch * 64 + c16 * 8) < p.c_in ? 16u : 0u;
+            const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
+            const uint32_t sb = a_base + ar.stage * stage_bytes + t * kTileBytes + (uint32_t)row0 * 128u;
+            const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+            // table entries are -1 for a missing neighbour and for rows past n_out
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
+                         xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
+            cp_async_arrive_noinc(&a_full[ar.stage]);
           }
+          ar.advance(S);
         }
-        ir = irt;
+        seen |= bits;
+        ir.advance(kIdxSlots);
       }
+      ++it;
     }
-  } else if (warp == 9) {
-    // ===================== MMA issuer =====================
-    uint8_t *sched = sched_all + 5 * kMaxK;
-    const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
-    // descriptor template: SBO = 1024 B (8-row atoms), LBO = 16 B (unused for one
-    // 128-byte K atom), version 1, SWIZZLE_128B; the start address is added per MMA
-    const uint64_t desc0 = smem_desc_sw128(0, 16, 1024);
-    Ring ar, br;
-    uint32_t it = 0;
-    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x, ++it) {
-      const uint32_t h = it & 1u;
-      const int64_t tile0 = (int64_t)g * p.T;
-      fill_sched(sched, p, tile0, ntiles, lane);
-      mbar_wait(&t_empty[h], ((it >> 1) & 1u) ^ 1u);
-      tc_fence_after();
-      uint32_t fresh = 0xFu;   // tiles whose accumulator has not been written in this group
-      for (int k = 0; k < p.K; ++k) {
-        const uint32_t bits = sched[k];
-        if (!bits) continue;
-        for (int ch = 0; ch < p.nchunk; ++ch) {
-          mbar_wait(&b_full[br.stage], br.phase);
-          const int nks = min(4, (p.c_in - ch * 64) >> 4);
-          const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
+    // the stage after the last one carries the END ticket
+    for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
+      if (t == (team - nst * T & 3u)) mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
+      if (t == 0 && q == 0 && lane == 0) {
+        tickets[ar.stage] = kTkEnd;
+        mbar_arrive(&a_full[ar.stage]);
+      }
+      mbar_arrive(&a_full[ar.stage]);
+    }
+  } else if (warp == kWarpMma0) {
+    // ===================== MMA issuer: driven by tickets =====================
+    // The whole warp runs the loop converged on warp-uniform values (the ticket is
+    // broadcast with a shuffle), so that the descriptors live in uniform registers
+    // and one elected lane issues back-to-back UTCHMMA without per-operand R2UR.
+    {
+      const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
+      const uint32_t tm_base = __shfl_sync(0xffffffffu, tmem_base, 0);
+      // descriptor template: SBO = 1024 B (8-row atoms), LBO = 16 B (unused for one
+      // 128-byte K atom), version 1, SWIZZLE_128B; the start address is added per MMA
+      const uint64_t desc0 = smem_desc_sw128(0, 16, 1024);
+      uint32_t s = 0, ph = 0, bs = 0, bph = 0;
+      for (;;) {
+        mbar_wait(&a_full[s], ph);
+        const uint32_t tk = __shfl_sync(0xffffffffu, *(volatile uint32_t *)&tickets[s], 0);
+        if (tk & kTkEnd) break;
+        const uint32_t h = (tk >> 8) & 1u;
+        if (tk & kTkGroupBegin) mbar_wait(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
+        mbar_wait(&b_full[bs], bph);
+        tc_fence_after();
+        const uint64_t bd0 = desc0 | (uint64_t)(((b_base + bs * b_bytes) & 0x3FFFFu) >> 4);
+        const uint32_t d0 = tm_base + h * 256u;
+        const uint32_t a0 = a_base + s * stage_bytes;
+        if (elect_one()) {
+          fence_proxy_async_smem();   // cp.async (generic proxy) writes -> tensor-core reads
 #pragma unroll
           for (int t = 0; t < kMaxT; ++t) {
-            if (t < p.T && ((bits >> t) & 1u)) {
-              mbar_wait(&a_full[ar.stage], ar.phase);
-              fence_proxy_async_smem();
-              tc_fence_after();
-              if (elect_one()) {
-                const uint32_t d = tmem_base + (uint32_t)(h * 256 + t * acc_stride);
-                const uint64_t ad0 = desc0 | (uint64_t)(((a_base + ar.stage * kStageBytes) & 0x3FFFFu) >> 4);
-                uint32_t acc = ((fresh >> t) & 1u) ? 0u : 1u;
-                for (int ks = 0; ks < nks; ++ks) {
-                  umma_f16(d, ad0 + (uint64_t)(ks * 2), bd0 + (uint64_t)(ks * 2), p.idesc, acc);
-                  acc = 1u;
-                }
-                umma_commit(&a_empty[ar.stage]);
+            if (!((tk >> t) & 1u)) continue;
+            const uint32_t d = d0 + (uint32_t)(t * acc_stride);
+            const uint64_t ad0 = desc0 | (uint64_t)(((a0 + (uint32_t)t * kTileBytes) & 0x3FFFFu) >> 4);
+            const uint32_t acc0 = (tk >> (4 + t)) & 1u;
+            if (kFull) {
+              umma_f16(d, ad0, bd0, p.idesc, acc0);
+              umma_f16(d, ad0 + 2, bd0 + 2, p.idesc, 1u);
+              umma_f16(d, ad0 + 4, bd0 + 4, p.idesc, 1u);
+              umma_f16(d, ad0 + 6, bd0 + 6, p.idesc, 1u);
+            } else {
+              const int nks = (int)((tk >> 16) & 7u);
+              uint32_t acc = acc0;
+              for (int ks = 0; ks < nks; ++ks) {
+                umma_f16(d, ad0 + (uint64_t)(ks * 2), bd0 + (uint64_t)(ks * 2), p.idesc, acc);
+                acc = 1u;
               }
-              __syncwarp();
-              fresh &= ~(1u << t);
-              ar.advance(S);
             }
           }
-          if (elect_one()) umma_commit(&b_empty[br.stage]);
-          __syncwarp();
-          br.advance(kBStages);
+          umma_commit(&a_empty[s]);
+          umma_commit(&b_empty[bs]);
+          if (tk & kTkGroupEnd) umma_commit(&t_full[h]);
         }
+        __syncwarp();
+        if (++bs == kBStages) { bs = 0; bph ^= 1u; }
+        if (++s == S) { s = 0; ph ^= 1u; }
       }
-      if (elect_one()) umma_commit(&t_full[h]);
-      __syncwarp();
     }
-  } else {
+    __syncwarp();
+  } else if (warp == kWarpWeights) {
     // ===================== weight loader =====================
-    uint8_t *sched = sched_all + 6 * kMaxK;
+    uint8_t *sched = sched_all + 1 * kMaxK;
     const uint32_t b_base = smem_u32(b_ring);
     Ring br;
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
@@ -368,7 +433,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
       for (int k = 0; k < p.K; ++k) {
         if (!sched[k]) continue;
         for (int ch = 0; ch < p.nchunk; ++ch) {
-          mbar_wait(&b_empty[br.stage], br.phase ^ 1u);
+          mbar_wait_warp(&b_empty[br.stage], br.phase ^ 1u);
           if (lane == 0) {
             const uint8_t *src = (const uint8_t *)p.bpack + (((size_t)sp * p.K + k) * p.nchunk + ch) * b_bytes;
             mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
@@ -383,7 +448,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == kWarpMma0) {
     tc_fence_after();
     tmem_dealloc_512(tmem_base);
   }
@@ -411,14 +476,15 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   pl.T = std::min(kMaxT, 256 / acc_stride);
   pl.W = (K + 31) / 32;
   const size_t b_bytes = (size_t)pl.NT * 128;
-  const size_t fixed = 1024 /*align slack*/ + kBStages * b_bytes + kIdxSlots * kTileM * 4 + 7 * kMaxK +
+  const size_t fixed = 1024 /*align slack*/ + kBStages * b_bytes + kIdxSlots * kMaxT * kTileM * 4 + kSchedCopies * kMaxK + 64 +
                        1024 /*barriers*/;
   const size_t budget = 227 * 1024;
-  int S = (int)((budget - fixed) / kStageBytes);
-  S = std::min(S, 12);
-  if (S < 3) return false;
+  const size_t stage_bytes = (size_t)pl.T * kTileBytes;
+  int S = (int)((budget - fixed) / stage_bytes);
+  S = std::min(S, 12);   // tickets[] holds 16
+  if (S < 3 || S * pl.T <= 4) return false;   // producer teams: consecutive stages of a team must be < S apart
   pl.a_stages = S;
-  pl.smem = fixed + (size_t)S * kStageBytes;
+  pl.smem = fixed + (size_t)S * stage_bytes;
   pl.bpack_bytes = align256s((size_t)nsplit * K * pl.nchunk * b_bytes);
   pl.mask_bytes = align256s((size_t)((n_out + kTileM - 1) / kTileM) * pl.W * 4);
   return true;
@@ -472,14 +538,21 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
-  static bool attr_set[2] = {false, false};
-  if (!attr_set[fmt]) {
-    MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set[fmt] = true;
+  const bool full = (c_in % 64) == 0;
+  static bool attr_set[2][2] = {{false, false}, {false, false}};
+  if (!attr_set[fmt][full]) {
+    if (full)
+      MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    else
+      MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[fmt][full] = true;
   }
   const int gx = (int)std::min<int64_t>((int64_t)p.ngroups, std::max(1, num_sms() / pl.nsplit));
   dim3 grid(gx, pl.nsplit);
-  k_conv_tc<T><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+  if (full)
+    k_conv_tc<T, true><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+  else
+    k_conv_tc<T, false><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
   MK_LAUNCH_CHECK();
   return MK_OK;
 }

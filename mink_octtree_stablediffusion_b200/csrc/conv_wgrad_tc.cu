@@ -158,7 +158,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
             const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
             int4 iv[8];
             if (real) {
-              mbar_wait(&i_full[ir.stage], ir.phase);
+              mbar_wait_warp(&i_full[ir.stage], ir.phase);
               const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + ir.stage * kTileM + rsub * 32);
 #pragma unroll
               for (int qq = 0; qq < 8; ++qq) iv[qq] = ip[qq];
@@ -168,7 +168,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
 #pragma unroll
               for (int qq = 0; qq < 8; ++qq) iv[qq] = make_int4(-1, -1, -1, -1);
             }
-            mbar_wait(&a_empty[ar.stage], ar.phase ^ 1u);
+            mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
             const uint32_t sb = a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)rsub * 4096u;
             uint32_t sbx[8];
 #pragma unroll
@@ -188,7 +188,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       }
     }
     // ===================== epilogue: TMEM -> fp32 partial =====================
-    mbar_wait(done, 0u);
+    mbar_wait_warp(done, 0u);
     tc_fence_after();
     const uint32_t inited = *(volatile uint32_t *)inited_slot;
     float *part = p.partial + (size_t)xs * p.K * p.c_in * p.c_out;
@@ -226,7 +226,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
         for (int hf = 0; hf < 2; ++hf) {
           if (!((ts.panels >> (2 * u + hf)) & 1u)) continue;
           const int k = (2 * (j0 + u) + hf) / p.pa;
-          mbar_wait(&i_empty[ir.stage], ir.phase ^ 1u);
+          mbar_wait_warp(&i_empty[ir.stage], ir.phase ^ 1u);
           if (lane == 0) {
             const int32_t *src = p.nbr + (int64_t)k * p.ld + (int64_t)tile * kTileM;
             mbar_arrive_expect_tx(&i_full[ir.stage], kTileM * 4);
@@ -248,11 +248,11 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
       const TileSched ts = tile_sched(p, tile, j0, npair_cta);
       if (!ts.pairs) continue;
-      mbar_wait(&b_full[br.stage], br.phase);
+      mbar_wait_warp(&b_full[br.stage], br.phase);
       const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
       for (int u = 0; u < npair_cta; ++u) {
         if (!((ts.pairs >> u) & 1u)) continue;
-        mbar_wait(&a_full[ar.stage], ar.phase);
+        mbar_wait_warp(&a_full[ar.stage], ar.phase);
         fence_proxy_async_smem();
         tc_fence_after();
         if (elect_one()) {
@@ -288,7 +288,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
       const TileSched ts = tile_sched(p, tile, j0, npair_cta);
       if (!ts.pairs) continue;
-      mbar_wait(&b_empty[br.stage], br.phase ^ 1u);
+      mbar_wait_warp(&b_empty[br.stage], br.phase ^ 1u);
       if (lane == 0) {
         mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
         for (int pn = 0; pn < p.pb; ++pn)

@@ -54,10 +54,16 @@ def main():
     ap.add_argument("--what", default="insert,kmap,fwd,dgrad,wgrad")
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--shuffle", type=int, default=0, help="1: random row order instead of sorted")
+    ap.add_argument("--dense", type=int, default=0, help="S: dense SxSxS cube instead of the sphere surface")
     args = ap.parse_args()
     what = set(args.what.split(","))
     dt = {"bf16": torch.bfloat16, "f16": torch.float16, "f32": torch.float32}[args.dtype]
-    c = sphere(args.r)
+    if args.dense:
+        S_ = args.dense
+        g3 = np.stack(np.meshgrid(np.arange(S_), np.arange(S_), np.arange(S_), indexing="ij"), -1).reshape(-1, 3)
+        c = np.concatenate([np.zeros((len(g3), 1), np.int32), g3.astype(np.int32)], 1)
+    else:
+        c = sphere(args.r)
     if args.shuffle:
         c = c[np.random.default_rng(1).permutation(len(c))]
     n = len(c)
