@@ -44,6 +44,10 @@ extern unsigned long long g_launch_count;
 int scan_block_sums(int32_t *block_sums, int64_t nblocks, int batch,
                     int64_t *total_dev, cudaStream_t st);
 
+// 4 words of mapped host memory a timed-out mbarrier wait reports into
+// (sm100.cuh); device pointer or nullptr.  mk_last_error() decodes it.
+unsigned int *hang_report_device_ptr();
+
 inline int num_sms() {
   static int n = 0;
   if (n == 0) {

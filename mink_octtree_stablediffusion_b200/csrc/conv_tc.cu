@@ -457,6 +457,16 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
+static int arm_hang_report() {
+  static bool done = false;
+  if (!done) {
+    unsigned int *d = hang_report_device_ptr();
+    MK_CUDA(cudaMemcpyToSymbol(sm100::mk_hang_slot, &d, sizeof(d)));
+    done = true;
+  }
+  return MK_OK;
+}
+
 struct TCPlan {
   int nsplit, NT, nchunk, T, W, a_stages;
   size_t smem, bpack_bytes, mask_bytes;
@@ -538,6 +548,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
+  { int rc = arm_hang_report(); if (rc) return rc; }
   const bool full = (c_in % 64) == 0;
   static bool attr_set[2][2] = {{false, false}, {false, false}};
   if (!attr_set[fmt][full]) {

@@ -23,11 +23,12 @@
 // each CTA writes its fp32 partial to the workspace and a second kernel sums
 // the X partials in a fixed order.
 //
-// CTA roles (224 threads, 1 CTA / SM):
-//   warps 0-3  gather producers, then the epilogue (TMEM -> fp32 partial)
-//   warp  4    neighbour-index prefetch (bulk copies into a smem ring)
-//   warp  5    MMA issuer
-//   warp  6    dy tile loader (TMA)
+// CTA roles (608 threads, 1 CTA / SM):
+//   warps 0-15  gather producers (four teams of four warps, one panel per team
+//               at a time); warps 0-3 then run the epilogue (TMEM -> fp32 partial)
+//   warp  16    neighbour-index prefetch (bulk copies into a smem ring)
+//   warp  17    MMA issuer
+//   warp  18    dy tile loader (TMA)
 #include <algorithm>
 
 #include "common.cuh"
@@ -41,8 +42,10 @@ namespace wg {
 constexpr int kTileM = 128;
 constexpr int kPanelBytes = kTileM * 128;   // [128 rows x 64 ch] 16-bit
 constexpr int kStageBytes = 2 * kPanelBytes;
-constexpr int kThreads = 224;
-constexpr int kGatherWarps = 4;
+constexpr int kGatherTeams = 4;
+constexpr int kGatherWarps = 4 * kGatherTeams;   // a team of 4 warps fills one panel (32 rows per warp)
+constexpr int kWarpIdx = kGatherWarps, kWarpMma = kGatherWarps + 1, kWarpDy = kGatherWarps + 2;
+constexpr int kThreads = 32 * (kGatherWarps + 3);
 constexpr int kIdxSlots = 32;
 constexpr int kMaxUnits = 16;
 
@@ -120,15 +123,15 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
   const int xs = blockIdx.x;
 
   if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 64); mbar_init(&a_empty[s], 1); }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 256); mbar_init(&a_empty[s], 1); }
     for (uint32_t s = 0; s < NBUF; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], 1); }
+    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], 4); }
     mbar_init(done, 1);
     *inited_slot = 0u;
     fence_barrier_init();
   }
-  if (warp == 6 && lane == 0) tma_prefetch_desc(&tmap_dy);
-  if (warp == 5) tmem_alloc_512(tmem_slot);
+  if (warp == kWarpDy && lane == 0) tma_prefetch_desc(&tmap_dy);
+  if (warp == kWarpMma) tmem_alloc_512(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -136,12 +139,17 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
 
   if (warp < kGatherWarps) {
     // ===================== gather producers =====================
-    // one work item = one panel; items are dealt round-robin to the four warps.
-    // lane = (rsub, c16): instruction i moves 16-byte chunk c16 of panel rows
-    // rsub*32 + i (four 128-byte feature rows per warp instruction)
+    // one work item = one panel; items are dealt round-robin to the four teams
+    // (a team's consecutive panels are 4 apart = 2 stages < S: alias-free parity
+    // waits with in-order release).  Warp q of a team moves panel rows
+    // [32q, 32q+32); lane = (rsub, c16): instruction i moves 16-byte chunk c16 of
+    // rows 32q + 8*rsub + i (four 128-byte feature rows per warp instruction)
     const uint32_t a_base = smem_u32(a_ring);
     const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
+    const uint32_t team = (uint32_t)warp >> 2;
+    const int q = warp & 3;
     const int c16 = lane & 7, rsub = lane >> 3;
+    const int row0 = 32 * q + 8 * rsub;
     Ring ir, ar;
     uint32_t e = 0;
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
@@ -150,36 +158,28 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
         if (!((ts.pairs >> u) & 1u)) continue;
         for (int hf = 0; hf < 2; ++hf, ++e) {
           const bool real = (ts.panels >> (2 * u + hf)) & 1u;
-          const bool mine = (e & (kGatherWarps - 1)) == (uint32_t)warp;
-          if (mine) {
-            const int q = 2 * (j0 + u) + hf;
-            const int pi = q % p.pa;
+          if ((e & (kGatherTeams - 1)) == team) {
+            const int qq = 2 * (j0 + u) + hf;
+            const int pi = qq % p.pa;
             const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
             const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
-            int4 iv[8];
+            int4 i0 = make_int4(-1, -1, -1, -1), i1 = i0;
             if (real) {
               mbar_wait_warp(&i_full[ir.stage], ir.phase);
-              const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + ir.stage * kTileM + rsub * 32);
-#pragma unroll
-              for (int qq = 0; qq < 8; ++qq) iv[qq] = ip[qq];
+              const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + ir.stage * kTileM + row0);
+              i0 = ip[0];
+              i1 = ip[1];
               __syncwarp();
               if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
-            } else {
-#pragma unroll
-              for (int qq = 0; qq < 8; ++qq) iv[qq] = make_int4(-1, -1, -1, -1);
             }
             mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
-            const uint32_t sb = a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)rsub * 4096u;
-            uint32_t sbx[8];
+            const uint32_t sb =
+                a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)row0 * 128u;
+            const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
 #pragma unroll
-            for (int j = 0; j < 8; ++j) sbx[j] = sb + (uint32_t)((c16 ^ j) << 4);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              const int32_t ri = (i & 3) == 0 ? iv[i >> 2].x : (i & 3) == 1 ? iv[i >> 2].y
-                                 : (i & 3) == 2 ? iv[i >> 2].z : iv[i >> 2].w;
-              cp_async16(sbx[i & 7] + (uint32_t)i * 128u, xb + (size_t)(uint32_t)max(ri, 0) * row_bytes,
-                         ri >= 0 ? szok : 0u);
-            }
+            for (int i = 0; i < 8; ++i)
+              cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
+                         xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
             cp_async_arrive_noinc(&a_full[ar.stage]);
           }
           if (real) ir.advance(kIdxSlots);
@@ -187,6 +187,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
         ar.advance(S);
       }
     }
+    if (warp >= 4) goto done_role;   // only warps 0-3 (TMEM lane quarters) run the epilogue
     // ===================== epilogue: TMEM -> fp32 partial =====================
     mbar_wait_warp(done, 0u);
     tc_fence_after();
@@ -216,7 +217,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       }
     }
     tc_fence_before();
-  } else if (warp == 4) {
+  } else if (warp == kWarpIdx) {
     // ===================== neighbour-index prefetch =====================
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
@@ -237,7 +238,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == kWarpMma) {
     // ===================== MMA issuer =====================
     const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
     // MN-major SW128 operands: LBO = distance between 64-channel panels,
@@ -300,9 +301,10 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     }
   }
 
+done_role:
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == kWarpMma) {
     tc_fence_after();
     tmem_dealloc_512(tmem_base);
   }
@@ -327,6 +329,16 @@ __global__ void k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
+static int arm_hang_report() {
+  static bool done = false;
+  if (!done) {
+    unsigned int *d = hang_report_device_ptr();
+    MK_CUDA(cudaMemcpyToSymbol(sm100::mk_hang_slot, &d, sizeof(d)));
+    done = true;
+  }
+  return MK_OK;
+}
+
 namespace {
 struct WPlan {
   int pa, npairs, nsplit, NB, nbpad, pb, U, G, ppg, a_stages, b_bufs, ntiles, X, W;
@@ -414,6 +426,7 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, 
   p.a_stages = pl.a_stages; p.b_bufs = pl.b_bufs;
   p.ntiles = pl.ntiles; p.X = pl.X;
   p.idesc = idesc_f16(dtype == MK_BF16 ? 1 : 0, kTileM, pl.NB, 1, 1);
+  { int rc = arm_hang_report(); if (rc) return rc; }
   static bool attr_set = false;
   if (!attr_set) {
     MK_CUDA(cudaFuncSetAttribute(k_conv_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));

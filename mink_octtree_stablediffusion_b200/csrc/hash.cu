@@ -29,8 +29,32 @@ void set_error(const char *fmt, ...) {
   va_end(ap);
 }
 
+static unsigned int *g_hang_host = nullptr, *g_hang_dev = nullptr;
+
+unsigned int *hang_report_device_ptr() {
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void *h = nullptr, *d = nullptr;
+    if (cudaHostAlloc(&h, 16, cudaHostAllocMapped) == cudaSuccess &&
+        cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
+      g_hang_host = (unsigned int *)h;
+      g_hang_dev = (unsigned int *)d;
+      memset(h, 0, 16);
+    } else {
+      (void)cudaGetLastError();
+    }
+  }
+  return g_hang_dev;
+}
+
 int cuda_fail(cudaError_t e, const char *what) {
-  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  if (g_hang_host && g_hang_host[0] == 0xDEADBA44u)
+    set_error("CUDA error %d (%s) at %s; pipeline wait timed out in block (%u,%u) warp %u on mbarrier smem 0x%x parity %u",
+              (int)e, cudaGetErrorString(e), what, g_hang_host[1] & 0xFFFFu, g_hang_host[1] >> 16, g_hang_host[2],
+              g_hang_host[3] >> 1, g_hang_host[3] & 1u);
+  else
+    set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return MK_ECUDA;
 }
 

@@ -6,7 +6,6 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
-#include <stdio.h>
 
 namespace mk {
 namespace sm100 {
@@ -56,17 +55,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a pipeline bug must surface as an error (trap -> sticky CUDA
-// error reported through mk_last_error), never as a hung GPU.
-static __device__ __noinline__ void mbar_timeout(uint64_t *bar, uint32_t parity) {
-  if ((threadIdx.x & 31) == (unsigned)(__ffs(__activemask()) - 1))
-    printf("mink_b200: mbarrier wait timed out (block %d,%d warp %d, barrier smem 0x%x, parity %u)\n",
-           (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), smem_u32(bar), parity);
-  // give the other stalled warps of the CTA time to report before the context dies
-  const long long t0 = clock64();
-  while (clock64() - t0 < 1000000000LL) {
-  }
-  __trap();
-}
+// error, reported by the next API call), never as a hung GPU.  The report goes
+// to a word of mapped host memory (it survives the dead context); everything is
+// inline - a call in this path would force spills into the hot loops.
+static __device__ unsigned int *mk_hang_slot = nullptr;   // set once per translation unit by the launcher
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int budget = 1) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
@@ -74,8 +66,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int bu
   while (!mbar_try_wait(bar, parity)) {
     if ((++spins & 0xFFFFu) == 0) {                   // clock read off the common path
       const long long now = clock64();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 10000000000LL * budget) mbar_timeout(bar, parity);   // ~5 s
+      if (t0 == 0) {
+        t0 = now;
+      } else if (now - t0 > 10000000000LL * budget) {  // ~5 s
+        unsigned int *h = mk_hang_slot;
+        if (h) {
+          h[1] = blockIdx.x | (blockIdx.y << 16);
+          h[2] = threadIdx.x >> 5;
+          h[3] = (smem_u32(bar) << 1) | parity;
+          h[0] = 0xDEADBA44u;
+          __threadfence_system();
+        }
+        asm volatile("trap;");
+      }
     }
   }
 }
@@ -88,25 +91,6 @@ __device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, uint32_t parity, i
   mbar_wait(bar, parity, budget);
   __syncwarp();
 }
-// Wait of a role that is normally far ahead of (or far behind) its partner: one
-// lane polls with a sleep between polls so that the warp stays off the issue
-// ports and the barrier unit; the other lanes park on the warp barrier.
-__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity, uint32_t sleep_ns, int budget = 1) {
-  if ((threadIdx.x & 31) == 0) {
-    uint32_t spins = 0;
-    long long t0 = 0;
-    while (!mbar_try_wait(bar, parity)) {
-      __nanosleep(sleep_ns);
-      if ((++spins & 0x3FFFu) == 0) {
-        const long long now = clock64();
-        if (t0 == 0) t0 = now;
-        else if (now - t0 > 10000000000LL * budget) mbar_timeout(bar, parity);
-      }
-    }
-  }
-  __syncwarp();
-}
-
 // ---- async copies -----------------------------------------------------------
 // 16-byte LDGSTS; src_bytes == 0 writes 16 zero bytes without touching memory
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src, uint32_t src_bytes) {
