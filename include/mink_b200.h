@@ -62,8 +62,10 @@ int mk_has_tcgen05(void);
  * cudf concurrent_unordered_map kernels behind it (pybind/extern.hpp:779;
  * MinkowskiCoordinateManager.py:153-179).
  *
- * The table is `capacity` 16-byte slots {uint64 key, uint32 row, uint32 pad};
- * capacity is a power of two from mk_hash_capacity(n) (>= 2n, <= 50% load).
+ * The table is capacity*16 bytes (32-byte aligned): capacity/2 buckets of one
+ * 32-byte sector {uint64 run key, uint32 row[4], pad}, a bucket holding a run of
+ * 4 cells along the first spatial axis.  capacity is a power of two from
+ * mk_hash_capacity(n) (>= 4n, i.e. <= 50% bucket load in the worst case).
  * ---------------------------------------------------------------------- */
 int64_t mk_hash_capacity(int64_t n);
 /* bytes of scratch mk_map_insert needs for n rows */

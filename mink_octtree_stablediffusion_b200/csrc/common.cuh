@@ -64,14 +64,21 @@ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // ---- coordinate keys --------------------------------------------------------
 // One coordinate row (b, x, y, z) -> 64-bit key.  Unused trailing axes are 0.
-// key = b << 48 | (x+32768) << 32 | (y+32768) << 16 | (z+32768).
+// key = b << 48 | (x+32768) << 32 | (y+32768) << 16 | (z+32768); the hash table
+// is keyed by runs of 4 cells along x (run_key below).
 constexpr uint64_t kEmptyKey = 0xFFFFFFFFFFFFFFFFull;  // b=65535 is reserved
 
-struct __align__(16) Slot {
+// A bucket is one aligned 32-byte sector and holds a RUN of 4 cells along the
+// first spatial axis: key = (b, x>>2, y, z), row[x&3] = compact row id (or
+// 0xFFFFFFFF).  Kernel offsets enumerate that axis fastest, so the 3 (or 2, 4,
+// 5 ...) neighbours of a kernel row cost one sector — two when the run
+// boundary is crossed — instead of one sector each.
+struct __align__(32) Bucket {
   unsigned long long key;
-  uint32_t row;
-  uint32_t pad;
+  uint32_t row[4];
+  uint32_t pad[2];
 };
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;
 
 __host__ __device__ __forceinline__ bool coord_in_range(int b, int x, int y,
                                                         int z) {
@@ -87,14 +94,25 @@ __host__ __device__ __forceinline__ uint64_t pack_key(int b, int x, int y,
          (uint64_t)(uint32_t)((z + 32768) & 0xFFFF);
 }
 
-// 64-bit finaliser (splitmix64 / murmur3 fmix style)
-__host__ __device__ __forceinline__ uint32_t hash_key(uint64_t k) {
-  k ^= k >> 33;
-  k *= 0xff51afd7ed558ccdull;
-  k ^= k >> 33;
-  k *= 0xc4ceb9fe1a85ec53ull;
-  k ^= k >> 33;
-  return (uint32_t)k;
+// home bucket of a run key {hi = b<<16 | run, lo = y<<16 | z}: multiply-add of
+// the two words, one xorshift-multiply round, TOP bits (mask = buckets-1, a
+// power of two minus one, >= 511).  5 integer instructions: the kernel-map
+// build evaluates it ~14 times per voxel.
+constexpr uint32_t kHashC1 = 0x9E3779B1u, kHashC2 = 0x85EBCA77u, kHashC3 = 0xC2B2AE3Du;
+
+__host__ __device__ __forceinline__ uint32_t hash_mix(uint32_t x) {
+  x ^= x >> 16;
+  x *= kHashC3;
+  return x;
+}
+
+__device__ __forceinline__ uint32_t bucket_home(uint32_t hi, uint32_t lo,
+                                                uint32_t mask) {
+  return hash_mix(hi * kHashC1 + lo * kHashC2) >> __clz(mask);
+}
+
+__device__ __forceinline__ uint32_t bucket_home(uint64_t key, uint32_t mask) {
+  return bucket_home((uint32_t)(key >> 32), (uint32_t)key, mask);
 }
 
 // read one coordinate row of ncols (<=4) int32 into b,x,y,z (missing = 0)
@@ -126,15 +144,48 @@ __device__ __forceinline__ void store_coord(int32_t *__restrict__ c, int64_t i,
   }
 }
 
-// probe the table for `key`; returns compact row or -1
-__device__ __forceinline__ int32_t table_find(const Slot *__restrict__ table,
-                                              uint32_t mask, uint64_t key) {
-  uint32_t h = hash_key(key) & mask;
+// ---- probing -----------------------------------------------------------------
+// Linear probing over buckets; a probe step is one LDG.256 of one sector.
+struct BucketRegs { uint32_t v[8]; };  // {key lo, key hi, row0..row3, pad, pad}
+
+__device__ __forceinline__ BucketRegs ldg_bucket(const Bucket *p) {
+  BucketRegs r;
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]),
+                 "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+               : "l"(p));
+  return r;
+}
+
+// key of the run that holds (b,x,y,z); the cell is row[x & 3] of its bucket
+__host__ __device__ __forceinline__ uint64_t run_key(int b, int x, int y,
+                                                     int z) {
+  return ((uint64_t)(uint32_t)(b & 0xFFFF) << 48) |
+         ((uint64_t)(uint32_t)(((x + 32768) & 0xFFFF) >> 2) << 32) |
+         ((uint64_t)(uint32_t)((y + 32768) & 0xFFFF) << 16) |
+         (uint64_t)(uint32_t)((z + 32768) & 0xFFFF);
+}
+
+__device__ __forceinline__ uint64_t bucket_key(const BucketRegs &s) {
+  return ((uint64_t)s.v[1] << 32) | s.v[0];
+}
+
+__device__ __forceinline__ int32_t bucket_row(const BucketRegs &s, int sub) {
+  const uint32_t lo = (sub & 1) ? s.v[3] : s.v[2];
+  const uint32_t hi = (sub & 1) ? s.v[5] : s.v[4];
+  return (int32_t)((sub & 2) ? hi : lo);  // kNoRow reads as -1
+}
+
+// probe the table for cell (b,x,y,z); returns compact row or -1
+__device__ __forceinline__ int32_t table_find(const Bucket *__restrict__ table,
+                                              uint32_t mask, int b, int x,
+                                              int y, int z) {
+  const uint64_t key = run_key(b, x, y, z);
+  uint32_t h = bucket_home(key, mask);
   while (true) {
-    // one 16-byte load: key + row together
-    const uint4 s = __ldg(reinterpret_cast<const uint4 *>(table + h));
-    const uint64_t k = ((uint64_t)s.y << 32) | s.x;
-    if (k == key) return (int32_t)s.z;
+    const BucketRegs s = ldg_bucket(table + h);
+    const uint64_t k = bucket_key(s);
+    if (k == key) return bucket_row(s, x & 3);
     if (k == kEmptyKey) return -1;
     h = (h + 1) & mask;
   }

@@ -7,11 +7,11 @@
 // find_coordinate, stride_copy, kernel_region_insert, origin_map_kernel,
 // prune_copy_and_insert.
 //
-// Design: 16-byte slots {u64 key, u32 row}, linear probing, <= 50 % load, so a
-// probe is one 16-B load and two slots share a 32-B sector.  Duplicates are
-// resolved deterministically (atomicMin on the row => first occurrence wins),
-// and compaction is an ordered block scan built from warp ballots, so
-// unique_index is ascending without any sort.
+// Design: 32-byte buckets {u64 run key, u32 row[4]} (common.cuh), one aligned
+// sector each, linear probing over buckets, <= 50 % bucket load.  A "slot" is
+// bucket*4 + (x&3).  Duplicates are resolved deterministically (atomicMin on the
+// row => first occurrence wins), and compaction is an ordered block scan built
+// from warp ballots, so unique_index is ascending without any sort.
 #include <stdarg.h>
 #include <string.h>
 
@@ -63,15 +63,19 @@ constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;  // rows per block
 
 // ---------------------------------------------------------------------------
-__global__ void k_table_clear(uint4 *__restrict__ table, int64_t capacity) {
+__global__ void k_table_clear(uint4 *__restrict__ table, int64_t n16) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < capacity;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16;
        i += stride)
-    table[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u);
+    table[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+}
+
+__device__ __forceinline__ uint32_t *slot_row(Bucket *table, int32_t slot) {
+  return &table[slot >> 2].row[slot & 3];
 }
 
 __global__ void k_insert(const int32_t *__restrict__ coords, int64_t n,
-                         int ncols, Slot *__restrict__ table, uint32_t mask,
+                         int ncols, Bucket *__restrict__ table, uint32_t mask,
                          int32_t *__restrict__ slot_of_row,
                          int32_t *__restrict__ status) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -83,16 +87,16 @@ __global__ void k_insert(const int32_t *__restrict__ coords, int64_t n,
     slot_of_row[i] = -1;
     return;
   }
-  const unsigned long long key = pack_key(b, x, y, z);
-  uint32_t h = hash_key(key) & mask;
+  const unsigned long long key = run_key(b, x, y, z);
+  uint32_t h = bucket_home(key, mask);
   for (uint32_t probes = 0; probes <= mask; ++probes) {
-    // cheap pre-check avoids most CAS (a slot's key never changes once set,
+    // cheap pre-check avoids most CAS (a bucket's key never changes once set,
     // so a stale read can only show "empty", which the CAS then corrects)
     unsigned long long old = *(volatile unsigned long long *)&table[h].key;
     if (old == kEmptyKey) old = atomicCAS(&table[h].key, kEmptyKey, key);
     if (old == kEmptyKey || old == key) {
-      atomicMin(&table[h].row, (uint32_t)i);
-      slot_of_row[i] = (int32_t)h;
+      atomicMin(&table[h].row[x & 3], (uint32_t)i);
+      slot_of_row[i] = (int32_t)(h * 4u + (uint32_t)(x & 3));
       return;
     }
     h = (h + 1) & mask;
@@ -103,7 +107,7 @@ __global__ void k_insert(const int32_t *__restrict__ coords, int64_t n,
 
 // first_of_row[i] = original row that owns i's key; block_sums[b] = #firsts
 __global__ void __launch_bounds__(kScanThreads)
-k_first_count(const Slot *__restrict__ table,
+k_first_count(Bucket *__restrict__ table,
               const int32_t *__restrict__ slot_of_row, int64_t n,
               int32_t *__restrict__ first_of_row,
               int32_t *__restrict__ block_sums) {
@@ -116,7 +120,7 @@ k_first_count(const Slot *__restrict__ table,
     bool first = false;
     if (i < n) {
       const int32_t s = slot_of_row[i];
-      const int32_t f = s >= 0 ? (int32_t)table[s].row : -1;
+      const int32_t f = s >= 0 ? (int32_t)*slot_row(table, s) : -1;
       first_of_row[i] = f;
       first = (f == (int32_t)i);
     }
@@ -223,7 +227,7 @@ k_compact_first(const int32_t *__restrict__ coords, int ncols,
   }
 }
 
-__global__ void k_finalize(Slot *__restrict__ table,
+__global__ void k_finalize(Bucket *__restrict__ table,
                            const int32_t *__restrict__ slot_of_row,
                            const int32_t *__restrict__ first_of_row,
                            const int32_t *__restrict__ newid_of_first,
@@ -237,10 +241,10 @@ __global__ void k_finalize(Slot *__restrict__ table,
   }
   const int32_t id = newid_of_first[f];
   if (inverse_map) inverse_map[i] = id;
-  if (f == (int32_t)i) table[slot_of_row[i]].row = (uint32_t)id;
+  if (f == (int32_t)i) *slot_row(table, slot_of_row[i]) = (uint32_t)id;
 }
 
-__global__ void k_lookup(const Slot *__restrict__ table, uint32_t mask,
+__global__ void k_lookup(const Bucket *__restrict__ table, uint32_t mask,
                          const int32_t *__restrict__ query, int64_t nq,
                          int ncols, int32_t *__restrict__ rows) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -248,7 +252,7 @@ __global__ void k_lookup(const Slot *__restrict__ table, uint32_t mask,
   int b, x, y, z;
   load_coord(query, i, ncols, b, x, y, z);
   rows[i] = coord_in_range(b, x, y, z)
-                ? table_find(table, mask, pack_key(b, x, y, z))
+                ? table_find(table, mask, b, x, y, z)
                 : -1;
 }
 
@@ -389,9 +393,12 @@ const char *mk_last_error(void) { return g_err; }
 int mk_version(void) { return 100; }
 int64_t mk_launch_count(void) { return (int64_t)g_launch_count; }
 
+// capacity is counted in 16-byte units (table bytes = 16 * capacity): two per
+// bucket, and >= 2n buckets so that even a cloud with one cell per run stays at
+// <= 50 % bucket load
 int64_t mk_hash_capacity(int64_t n) {
   int64_t cap = 1024;
-  while (cap < 2 * n) cap <<= 1;
+  while (cap < 4 * n) cap <<= 1;
   return cap;
 }
 
@@ -408,11 +415,13 @@ int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
                   int64_t *n_unique_dev, int32_t *status_dev, void *stream) {
   MK_CHECK_ARG(ncols >= 2 && ncols <= 4, "ncols must be in [2,4] (D <= 3)");
   MK_CHECK_ARG(n >= 0 && n < (int64_t)0x7fffffff, "row count out of range");
-  MK_CHECK_ARG(capacity >= 2 * n && (capacity & (capacity - 1)) == 0 &&
-                   capacity <= ((int64_t)1 << 32),
-               "capacity must be a power of two >= 2n");
+  MK_CHECK_ARG(capacity >= 4 * n && capacity >= 1024 &&
+                   (capacity & (capacity - 1)) == 0 &&
+                   capacity <= ((int64_t)1 << 30),
+               "capacity must be a power of two >= max(4n, 1024)");
   MK_CHECK_ARG(table && n_unique_dev && status_dev && (workspace || n == 0),
                "null pointer");
+  MK_CHECK_ARG((uintptr_t)table % 32 == 0, "table must be 32-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   MK_CUDA(cudaMemsetAsync(status_dev, 0, sizeof(int32_t), st));
   {
@@ -432,12 +441,12 @@ int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
   int32_t *newid = (int32_t *)ws; ws += align256(n * 4);
   int32_t *block_sums = (int32_t *)ws;
   const int64_t nblk = ceil_div(n, kScanTile);
-  const uint32_t mask = (uint32_t)(capacity - 1);
+  const uint32_t mask = (uint32_t)(capacity / 2 - 1);  // buckets - 1
   k_insert<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(
-      coords, n, ncols, (Slot *)table, mask, slot_of_row, status_dev);
+      coords, n, ncols, (Bucket *)table, mask, slot_of_row, status_dev);
   MK_LAUNCH_CHECK();
   k_first_count<<<(unsigned)nblk, kScanThreads, 0, st>>>(
-      (const Slot *)table, slot_of_row, n, first_of_row, block_sums);
+      (Bucket *)table, slot_of_row, n, first_of_row, block_sums);
   MK_LAUNCH_CHECK();
   k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nblk, n_unique_dev);
   MK_LAUNCH_CHECK();
@@ -446,7 +455,7 @@ int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
       coords_out);
   MK_LAUNCH_CHECK();
   k_finalize<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(
-      (Slot *)table, slot_of_row, first_of_row, newid, n, inverse_map);
+      (Bucket *)table, slot_of_row, first_of_row, newid, n, inverse_map);
   MK_LAUNCH_CHECK();
   return MK_OK;
 }
@@ -454,12 +463,13 @@ int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
 int mk_map_lookup(const void *table, int64_t capacity, const int32_t *query,
                   int64_t nq, int ncols, int32_t *rows, void *stream) {
   MK_CHECK_ARG(ncols >= 2 && ncols <= 4, "ncols must be in [2,4]");
-  MK_CHECK_ARG(capacity > 0 && (capacity & (capacity - 1)) == 0,
-               "capacity must be a power of two");
+  MK_CHECK_ARG(capacity >= 1024 && (capacity & (capacity - 1)) == 0,
+               "capacity must be a power of two >= 1024");
   if (nq == 0) return MK_OK;
   MK_CHECK_ARG(table && query && rows, "null pointer");
   k_lookup<<<(unsigned)ceil_div(nq, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const Slot *)table, (uint32_t)(capacity - 1), query, nq, ncols, rows);
+      (const Bucket *)table, (uint32_t)(capacity / 2 - 1), query, nq, ncols,
+      rows);
   MK_LAUNCH_CHECK();
   return MK_OK;
 }

@@ -27,7 +27,7 @@ def test_prototypes_cover_header():
 
 def test_pure_host_entry_points(lib):
     assert lib.mk_version() >= 100
-    assert lib.mk_hash_capacity(1000) == 2048
+    assert lib.mk_hash_capacity(1000) == 4096
     assert lib.mk_hash_capacity(0) >= 1
     assert lib.mk_insert_workspace_bytes(1 << 20) > 3 * 4 * (1 << 20)
     assert lib.mk_select_workspace_bytes(10) > 0
