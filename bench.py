@@ -100,6 +100,9 @@ def cpu_sample(R: int, reps: int, seed: int = 0):
     n = len(c)
     offs = O.kernel_offsets([KS] * 3, [1, 1, 1])
     t0 = time.perf_counter()
+    # every host thread this process may use (torchrun exports OMP_NUM_THREADS=1 for its workers; ME's own
+    # default is min(cpu_count, 16-20), __init__.py:34-46)
+    CR.set_num_threads(len(os.sched_getaffinity(0)))
     cmap = CR.CoordMap(c)
     t1 = time.perf_counter()
     km = CR.KernelMap(cmap, c, offs)
@@ -200,7 +203,7 @@ def run_engine(args):
     out, gi, gw = step_resident()
     torch.cuda.synchronize()
     kmap = next(iter(mgr._kmaps.values()))
-    P = int(kmap.counts.sum().item())
+    P = int((kmap.nbr[:, :n] >= 0).sum().item())      # (in, out) pairs of the map
     conv_path = int(lib.mk_conv_last_path())
 
     def sync_all():
@@ -280,22 +283,32 @@ def run_engine(args):
     # ---- integer stages, timed alone (new map each iteration) ----------------
     stage = {}
     if rank == 0:
-        ins, kmb = [], []
-        for _ in range(5):
-            a, b, c2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        from mink_octtree_stablediffusion_b200 import backend_ops as _ops
+        ins, kmb, kme = [], [], []
+        busy = torch.empty((8192, 8192), dtype=torch.bfloat16, device=dev).normal_()
+        for _ in range(7):
+            a, b, c2, d2 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
             m2 = _C.CoordinateMapManagerGPU_c10()
+            torch.mm(busy, busy)     # ~1 ms of device work: the host runs ahead, the events time the device only
             a.record()
             k2, _maps = m2.insert_and_map(coords_d, [1, 1, 1], "")
             b.record()
+            # the table the conv kernels read (mk_kmap_build) ...
+            _ops._kernel_map(m2, k2, k2, kg.kernel_size, kg.kernel_stride, kg.kernel_dilation, kg.region_type,
+                             empty_off, False, False)
+            c2.record()
+            # ... and the (in, out) pair lists the Python API exports from it
             m2.kernel_map(k2, k2, kg.kernel_size, kg.kernel_stride, kg.kernel_dilation, kg.region_type, empty_off,
                           False, False)
-            c2.record()
+            d2.record()
             torch.cuda.synchronize()
             ins.append(a.elapsed_time(b))
             kmb.append(b.elapsed_time(c2))
+            kme.append(c2.elapsed_time(d2))
         K = KS ** 3
-        stage = {"hash_insert_ms": float(np.median(ins)), "kmap_build_export_ms": float(np.median(kmb)),
-                 "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n + 8 * P)}
+        stage = {"hash_insert_ms": float(np.median(ins)), "kmap_build_ms": float(np.median(kmb)),
+                 "kmap_pairs_export_ms": float(np.median(kme)),
+                 "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n)}
 
     # ---- reduce over ranks -----------------------------------------------------
     t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms], dtype=torch.float64, device=dev)
@@ -336,7 +349,7 @@ def run_engine(args):
         }
         if stage:
             line["stages"]["hash_insert_hbm_frac"] = stage["hash_insert_alg_bytes"] / (stage["hash_insert_ms"] * 1e-3) / 1e9 / pk["hbm"]
-            line["stages"]["kmap_hbm_frac"] = stage["kmap_alg_bytes"] / (stage["kmap_build_export_ms"] * 1e-3) / 1e9 / pk["hbm"]
+            line["stages"]["kmap_hbm_frac"] = stage["kmap_alg_bytes"] / (stage["kmap_build_ms"] * 1e-3) / 1e9 / pk["hbm"]
         if world == 1 and not args.no_cpu_baseline:
             s = cpu_sample(96, 3)
             line["cpu_baseline"] = {"value": s["n"] / s["step_s"], "unit": UNIT, "cores": s["cores"], "kind": "port",

@@ -17,6 +17,7 @@ PyTorch's current CUDA stream.
 from __future__ import annotations
 
 import ctypes
+import functools
 import enum
 import random
 import string
@@ -257,6 +258,13 @@ def region_offsets(kernel_size: Sequence[int], scale: Sequence[int], region_type
         _require(custom is not None and custom.numel() > 0, "CUSTOM region needs region_offsets")
         offs = custom.detach().cpu().numpy().astype(np.int64).reshape(-1, D)
         return offs * np.asarray(scale, dtype=np.int64)[None, :]
+    return _regular_offsets(tuple(int(k) for k in kernel_size), tuple(int(v) for v in scale), int(region_type))
+
+
+@functools.lru_cache(maxsize=256)
+def _regular_offsets(kernel_size: Tuple[int, ...], scale: Tuple[int, ...], region_type: int) -> np.ndarray:
+    D = len(kernel_size)
+    region_type = RegionType(region_type)
     axes = [np.arange(-(k // 2), k // 2 + 1) if k % 2 == 1 else np.arange(0, k) for k in kernel_size]
     if region_type == RegionType.HYPER_CUBE:
         grids = np.meshgrid(*axes[::-1], indexing="ij")          # slowest axis first
@@ -271,7 +279,9 @@ def region_offsets(kernel_size: Sequence[int], scale: Sequence[int], region_type
                     r[d] = int(v)
                     rows.append(r)
         offs = np.asarray(rows, dtype=np.int64)
-    return offs.astype(np.int64) * np.asarray(scale, dtype=np.int64)[None, :]
+    offs = offs.astype(np.int64) * np.asarray(scale, dtype=np.int64)[None, :]
+    offs.setflags(write=False)       # cached: callers negate / copy, never write in place
+    return offs
 
 
 # ---------------------------------------------------------------------------

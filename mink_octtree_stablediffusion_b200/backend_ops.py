@@ -23,12 +23,11 @@ def _build_table(mgr, out_map: _CoordMap, in_map: _CoordMap, offsets: np.ndarray
     ld = _pad_ld(out_map.n)
     dev = out_map.coords.device
     nbr = torch.empty((K, ld), dtype=torch.int32, device=dev)
-    counts = torch.empty(K, dtype=torch.int64, device=dev)
     offs_h = _host_i32(offsets)
+    # per-offset pair counts are not needed by the table form (the CSR export counts on its own)
     _lib.check(mgr._lib.mk_kmap_build(_ptr(out_map.coords), out_map.n, out_map.coords.shape[1], _ptr(in_map.table),
-                                      in_map.capacity, _np_ptr(offs_h), K, _ptr(nbr), ld,
-                                      ctypes.c_void_p(counts.data_ptr()), _stream()))
-    return _KernelMap(nbr, ld, in_map.n, out_map.n, K, counts, symmetric)
+                                      in_map.capacity, _np_ptr(offs_h), K, _ptr(nbr), ld, None, _stream()))
+    return _KernelMap(nbr, ld, in_map.n, out_map.n, K, None, symmetric)
 
 
 def _inverse_table(mgr, km: _KernelMap):

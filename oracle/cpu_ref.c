@@ -45,6 +45,7 @@ static inline void load4(const int32_t *coords, int64_t i, int ncols, int32_t *o
 typedef struct { slot_t *slots; uint64_t mask; } cmap_t;
 
 int cr_num_threads(void) { return omp_get_max_threads(); }
+void cr_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 void *cr_map_create(int64_t n) {
   cmap_t *m = (cmap_t *)malloc(sizeof(cmap_t));

@@ -25,6 +25,7 @@ def lib():
         l.cr_conv_backward.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         l.cr_num_threads.restype = C.c_int
+        l.cr_set_num_threads.argtypes = [C.c_int]
         _lib = l
     return _lib
 
@@ -89,3 +90,8 @@ def conv_backward(x: np.ndarray, dy: np.ndarray, w: np.ndarray, km: KernelMap):
 
 def num_threads() -> int:
     return int(lib().cr_num_threads())
+
+
+def set_num_threads(n: int) -> None:
+    """Override OMP_NUM_THREADS (torchrun exports 1 for its workers)."""
+    lib().cr_set_num_threads(int(n))

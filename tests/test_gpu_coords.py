@@ -109,6 +109,27 @@ def test_kernel_map_same_map(ks, scale):
     _check_kmap(c, c, O.kernel_offsets(ks, scale))
 
 
+@pytest.mark.parametrize("ks", [[2, 2, 2], [3, 3, 3], [4, 4, 4], [5, 3, 3]])
+def test_kernel_map_at_coordinate_limits(ks):
+    """Rows on the int16 borders: neighbours that would leave the key range are
+    absent (never aliased onto the opposite border), in both build kernels."""
+    rng = np.random.default_rng(5)
+    edge = np.array([-32768, -32767, -32766, -32765, -32764, 32763, 32764, 32765, 32766, 32767, -1, 0, 1], np.int64)
+    c = np.stack([rng.integers(0, 2, 4000), rng.choice(edge, 4000), rng.choice(edge, 4000),
+                  rng.choice(edge, 4000)], 1).astype(np.int32)
+    c[:200, 0] = 65534
+    c = np.unique(c, axis=0)
+    offs = O.kernel_offsets(ks, [1, 1, 1])
+    _check_kmap(c, c, offs)             # row-structured kernel
+    _check_kmap(c, c, -offs)            # mirrored order (transposed maps): general kernel
+
+
+@pytest.mark.parametrize("ncols,ks", [(2, [3]), (2, [5]), (3, [3, 3]), (3, [2, 2]), (3, [3, 1])])
+def test_kernel_map_low_dimension(ncols, ks):
+    c = np.unique(random_cloud(3000, 40 if ncols == 2 else 12, 3, seed=17, ncols=ncols), axis=0)
+    _check_kmap(c, c, O.kernel_offsets(ks, [1] * (ncols - 1)))
+
+
 def test_kernel_map_strided_and_inverse():
     c = O.sphere_surface(30, seed=3)
     s = O.stride_coords(c, [2, 2, 2])
