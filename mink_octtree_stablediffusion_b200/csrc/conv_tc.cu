@@ -49,9 +49,28 @@ constexpr int kWarpIdx = 4, kWarpWeights = 5, kWarpMma0 = 6, kWarpGather0 = kWar
 constexpr int kNumThreadsTC = 32 * (kWarpGather0 + kGatherWarps);
 constexpr int kSchedCopies = 2 + kGatherWarps;
 constexpr int kMaxT = 4;                   // tiles per group (256 TMEM columns / NT)
-constexpr int kIdxSlots = 4;               // ring of neighbour-index rows: one slot = the T*128 entries of a group under one offset
-constexpr int kBStages = 2;                // weight-image ring
+constexpr int kMaxIdxSlots = 8;            // ring of neighbour-index rows: one slot = the T*128 entries of a group under one offset
+constexpr int kMaxBStages = 8;             // weight-image ring
 constexpr int kMaxK = 128;
+
+// -DMK_TC_PROF: per-CTA cycle counters of where each role waits (development aid;
+// read back with mk_debug_prof_read).  Compiled out of the product build.
+#ifdef MK_TC_PROF
+__device__ unsigned long long g_prof[256 * 32];
+#define PROF_DECL(...) unsigned long long __VA_ARGS__
+#define PROF_NOW() clock64()
+#define PROF_T0(v) v = clock64()
+#define PROF_ADD(acc, t0) acc += clock64() - (t0)
+#define PROF_PUT(slot, v) g_prof[blockIdx.x * 32 + (slot)] = (v)
+#define PROF_INC(acc) ++acc
+#else
+#define PROF_DECL(...)
+#define PROF_NOW() 0
+#define PROF_T0(v)
+#define PROF_ADD(acc, t0)
+#define PROF_PUT(slot, v)
+#define PROF_INC(acc)
+#endif
 
 struct ConvTCParams {
   const void *x;          // [n_in, c_in] 16-bit
@@ -62,7 +81,7 @@ struct ConvTCParams {
   int64_t ld, n_out, n_in;
   int K, W, kflip;
   int c_in, c_out, nchunk, NT, T;
-  int a_stages;
+  int a_stages, b_stages, i_slots;
   int ngroups;
   uint32_t idesc;
 };
@@ -177,8 +196,10 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   uint8_t *a_ring = smem;
   const uint32_t stage_bytes = (uint32_t)p.T * kTileBytes;
   uint8_t *b_ring = a_ring + (size_t)S * stage_bytes;
+  const uint32_t kBStages = (uint32_t)p.b_stages, kIdxSlots = (uint32_t)p.i_slots;
+  const uint32_t idx_slot = (uint32_t)p.T * kTileM;   // entries per slot
   int32_t *idx_ring = (int32_t *)(b_ring + kBStages * b_bytes);
-  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * kMaxT * kTileM);   // per-role copies x kMaxK
+  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * idx_slot);   // per-role copies x kMaxK
   uint32_t *tickets = (uint32_t *)(sched_all + kSchedCopies * kMaxK);   // [S]
   uint64_t *bars = (uint64_t *)(tickets + 16);
   uint64_t *a_full = bars, *a_empty = a_full + S;
@@ -194,8 +215,8 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
 
   if (threadIdx.x == 0) {
     for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u); mbar_init(&a_empty[s], 1); }
-    for (int s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
+    for (uint32_t s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (uint32_t s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
     for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
     fence_barrier_init();
   }
@@ -208,6 +229,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   if (warp < 4) {
     // ===================== epilogue =====================
     uint32_t it = 0;   // counts the groups that have any work (the others never reach the MMA thread)
+    PROF_DECL(pe_wait = 0, pe_work = 0, pe_t0 = 0, pe_t1 = 0;)
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
       const uint32_t h = it & 1u;
       const int64_t tile0 = (int64_t)g * p.T;
@@ -216,9 +238,12 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         if (tile0 + t < ntiles)
           for (int wi = 0; wi < p.W; ++wi) any |= __ldg(p.mask + (tile0 + t) * p.W + wi);
       if (any) {
+        PROF_T0(pe_t0);
         mbar_wait_warp(&t_full[h], (it >> 1) & 1u, 3);   // outermost wait: report inner stalls first
         tc_fence_after();
+        PROF_ADD(pe_wait, pe_t0);
       }
+      PROF_T0(pe_t1);
       for (int t = 0; t < p.T; ++t) {
         const int64_t tile = tile0 + t;
         if (tile >= ntiles) break;
@@ -251,6 +276,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
           }
         }
       }
+      PROF_ADD(pe_work, pe_t1);
       if (any) {
         tc_fence_before();
         __syncwarp();
@@ -258,6 +284,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         ++it;
       }
     }
+    if (warp == 0 && lane == 0) { PROF_PUT(0, pe_wait); PROF_PUT(1, pe_work); }
   } else if (warp == kWarpIdx) {
     // ===================== neighbour-index prefetch =====================
     // one slot of the idx ring per offset: the T*128 table entries of the group; the
@@ -265,6 +292,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     uint8_t *sched = sched_all + 0 * kMaxK;
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
+    PROF_DECL(pi_wait = 0, pi_t0 = 0;)
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
       const int64_t tile0 = (int64_t)g * p.T;
       fill_sched(sched, p, tile0, ntiles, lane);
@@ -272,19 +300,22 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         const uint32_t bits = sched[k];
         if (!bits) continue;
         const int kk = p.kflip ? p.K - 1 - k : k;
+        PROF_T0(pi_t0);
         mbar_wait_warp(&i_empty[ir.stage], ir.phase ^ 1u);
+        PROF_ADD(pi_wait, pi_t0);
         if (lane == 0) {
           // the T tiles of a group are consecutive rows of the table: one copy
           const int64_t first = tile0 * kTileM;
           const uint32_t bytes = (uint32_t)min((int64_t)p.T * kTileM, p.ld - first) * 4u;
           const int32_t *src = p.nbr + (int64_t)kk * p.ld + first;
           mbar_arrive_expect_tx(&i_full[ir.stage], bytes);
-          bulk_g2s(i_base + ir.stage * (kMaxT * kTileM * 4), src, bytes, &i_full[ir.stage]);
+          bulk_g2s(i_base + ir.stage * (idx_slot * 4u), src, bytes, &i_full[ir.stage]);
         }
         __syncwarp();
         ir.advance(kIdxSlots);
       }
     }
+    if (lane == 0) PROF_PUT(2, pi_wait);
   } else if (warp >= kWarpGather0) {
     // ===================== gather producers (LDGSTS) =====================
     // Four teams of four warps.  Tile slot t of stage number n (stages are counted
@@ -308,6 +339,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     Ring ir, ar;                                   // idx slot of the row's first tile / current A stage
     uint32_t nst = 0;                              // stages so far
     uint32_t it = 0;                               // groups with work so far
+    PROF_DECL(pg_we = 0, pg_wi = 0, pg_iss = 0, pg_t0 = 0, pg_n = 0;)
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
       const int64_t tile0 = (int64_t)g * p.T;
       const uint32_t n_stages = fill_sched(sched, p, tile0, ntiles, lane) * (uint32_t)p.nchunk;
@@ -320,7 +352,12 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         for (int ch = 0; ch < p.nchunk; ++ch, ++nst, ++done) {
           bool waited = false;
           for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
-            if (!waited) { mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u); waited = true; }
+            if (!waited) {
+              PROF_T0(pg_t0);
+              mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
+              PROF_ADD(pg_we, pg_t0);
+              waited = true;
+            }
             if (t == 0 && q == 0 && lane == 0) {
               const uint32_t nks = kFull ? 4u : (uint32_t)min(4, (p.c_in - ch * 64) >> 4);
               uint32_t tk = tk_group | bits | ((ch > 0 ? 0xFu : seen) << 4) | (nks << 16);
@@ -334,9 +371,12 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
               continue;
             }
+            PROF_T0(pg_t0);
             mbar_wait_warp(&i_full[ir.stage], ir.phase);
+            PROF_ADD(pg_wi, pg_t0);
+            PROF_T0(pg_t0);
             const int4 *ip =
-                reinterpret_cast<const int4 *>(idx_ring + ir.stage * (kMaxT * kTileM) + t * kTileM + row0);
+                reinterpret_cast<const int4 *>(idx_ring + ir.stage * idx_slot + t * kTileM + row0);
             const int4 i0 = ip[0], i1 = ip[1];
             __syncwarp();
             if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
@@ -350,6 +390,8 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
                          xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
             cp_async_arrive_noinc(&a_full[ar.stage]);
+            PROF_ADD(pg_iss, pg_t0);
+            PROF_INC(pg_n);
           }
           ar.advance(S);
         }
@@ -358,6 +400,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
       }
       ++it;
     }
+    if (lane == 0 && q == 0) { PROF_PUT(8 + 4 * team, pg_we); PROF_PUT(9 + 4 * team, pg_wi); PROF_PUT(10 + 4 * team, pg_iss); PROF_PUT(11 + 4 * team, pg_n); }
     // the stage after the last one carries the END ticket
     for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
       if (t == (team - nst * T & 3u)) mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
@@ -379,19 +422,30 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
       // 128-byte K atom), version 1, SWIZZLE_128B; the start address is added per MMA
       const uint64_t desc0 = smem_desc_sw128(0, 16, 1024);
       uint32_t s = 0, ph = 0, bs = 0, bph = 0;
+      PROF_DECL(pm_wa = 0, pm_wt = 0, pm_wb = 0, pm_iss = 0, pm_n = 0, pm_t0 = 0, pm_start = PROF_NOW(), pm_f = 0, pm_m = 0, pm_c = 0;)
       for (;;) {
+        PROF_T0(pm_t0);
         mbar_wait(&a_full[s], ph);
+        PROF_ADD(pm_wa, pm_t0);
         const uint32_t tk = __shfl_sync(0xffffffffu, *(volatile uint32_t *)&tickets[s], 0);
         if (tk & kTkEnd) break;
         const uint32_t h = (tk >> 8) & 1u;
+        PROF_T0(pm_t0);
         if (tk & kTkGroupBegin) mbar_wait(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
+        PROF_ADD(pm_wt, pm_t0);
+        PROF_T0(pm_t0);
         mbar_wait(&b_full[bs], bph);
+        PROF_ADD(pm_wb, pm_t0);
+        PROF_T0(pm_t0);
         tc_fence_after();
         const uint64_t bd0 = desc0 | (uint64_t)(((b_base + bs * b_bytes) & 0x3FFFFu) >> 4);
         const uint32_t d0 = tm_base + h * 256u;
         const uint32_t a0 = a_base + s * stage_bytes;
         if (elect_one()) {
+          PROF_DECL(pq_t0 = clock64();)
           fence_proxy_async_smem();   // cp.async (generic proxy) writes -> tensor-core reads
+          PROF_ADD(pm_f, pq_t0);
+          PROF_T0(pq_t0);
 #pragma unroll
           for (int t = 0; t < kMaxT; ++t) {
             if (!((tk >> t) & 1u)) continue;
@@ -412,13 +466,27 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               }
             }
           }
+          PROF_ADD(pm_m, pq_t0);
+          PROF_T0(pq_t0);
           umma_commit(&a_empty[s]);
           umma_commit(&b_empty[bs]);
           if (tk & kTkGroupEnd) umma_commit(&t_full[h]);
+          PROF_ADD(pm_c, pq_t0);
         }
         __syncwarp();
+        PROF_ADD(pm_iss, pm_t0);
+        PROF_INC(pm_n);
         if (++bs == kBStages) { bs = 0; bph ^= 1u; }
         if (++s == S) { s = 0; ph ^= 1u; }
+      }
+      if (lane == 0) {
+        PROF_PUT(3, pm_wa); PROF_PUT(4, pm_wt); PROF_PUT(5, pm_wb); PROF_PUT(6, pm_iss); PROF_PUT(7, pm_n);
+        PROF_PUT(24, PROF_NOW() - pm_start);
+      }
+      {
+        // the elected lane's private counters (max over lanes: the others hold 0)
+        PROF_PUT(25, __reduce_max_sync(0xffffffffu, (unsigned)pm_f)); PROF_PUT(26, __reduce_max_sync(0xffffffffu, (unsigned)pm_m));
+        PROF_PUT(27, __reduce_max_sync(0xffffffffu, (unsigned)pm_c));
       }
     }
     __syncwarp();
@@ -468,7 +536,7 @@ static int arm_hang_report() {
 }
 
 struct TCPlan {
-  int nsplit, NT, nchunk, T, W, a_stages;
+  int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots;
   size_t smem, bpack_bytes, mask_bytes;
 };
 
@@ -484,10 +552,16 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   pl.nchunk = (c_in + 63) / 64;
   const int acc_stride = (pl.NT + 31) & ~31;
   pl.T = std::min(kMaxT, 256 / acc_stride);
+  pl.b_stages = 2;
+  pl.i_slots = 4;
+  // development knobs (tuning sweeps): MK_TC_T / MK_TC_BSTAGES / MK_TC_ISLOTS
+  if (const char *e = getenv("MK_TC_T")) pl.T = std::max(1, std::min(pl.T, atoi(e)));
+  if (const char *e = getenv("MK_TC_BSTAGES")) pl.b_stages = std::max(2, std::min(kMaxBStages, atoi(e)));
+  if (const char *e = getenv("MK_TC_ISLOTS")) pl.i_slots = std::max(2, std::min(kMaxIdxSlots, atoi(e)));
   pl.W = (K + 31) / 32;
   const size_t b_bytes = (size_t)pl.NT * 128;
-  const size_t fixed = 1024 /*align slack*/ + kBStages * b_bytes + kIdxSlots * kMaxT * kTileM * 4 + kSchedCopies * kMaxK + 64 +
-                       1024 /*barriers*/;
+  const size_t fixed = 1024 /*align slack*/ + pl.b_stages * b_bytes + (size_t)pl.i_slots * pl.T * kTileM * 4 +
+                       kSchedCopies * kMaxK + 64 + 1024 /*barriers*/;
   const size_t budget = 227 * 1024;
   const size_t stage_bytes = (size_t)pl.T * kTileBytes;
   int S = (int)((budget - fixed) / stage_bytes);
@@ -544,7 +618,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y;
   p.ld = ld; p.n_out = n_out; p.n_in = n_in; p.K = K; p.W = pl.W; p.kflip = kflip;
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
-  p.a_stages = pl.a_stages;
+  p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots;
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
@@ -587,6 +661,12 @@ int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kf
 }  // namespace mk
 
 extern "C" int mk_has_tcgen05(void) { return 1; }
+
+#ifdef MK_TC_PROF
+extern "C" int mk_debug_prof_read(unsigned long long *host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, mk::g_prof, sizeof(unsigned long long) * n);
+}
+#endif
 
 extern "C" int64_t mk_kmap_tile_mask_words(int K) { return (K + 31) / 32; }
 

@@ -55,6 +55,7 @@ def main():
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--shuffle", type=int, default=0, help="1: random row order instead of sorted")
     ap.add_argument("--dense", type=int, default=0, help="S: dense SxSxS cube instead of the sphere surface")
+    ap.add_argument("--sweep", default="", help="semicolon list of T,BSTAGES,ISLOTS settings of the conv kernel (dev knobs)")
     args = ap.parse_args()
     what = set(args.what.split(","))
     dt = {"bf16": torch.bfloat16, "f16": torch.float16, "f32": torch.float32}[args.dtype]
@@ -79,6 +80,16 @@ def main():
     w = (torch.randn(27, args.cin, args.cout, generator=g) / np.sqrt(27 * args.cin)).to(dt).cuda()
     mask = abi.tile_mask(nbr, n, ld, 27)
     fl = 2.0 * P * args.cin * args.cout
+    for cfg in [c_ for c_ in args.sweep.split(";") if c_]:
+        T_, B_, I_ = cfg.split(",")
+        os.environ["MK_TC_T"], os.environ["MK_TC_BSTAGES"], os.environ["MK_TC_ISLOTS"] = T_, B_, I_
+        t, _ = timed(lambda: abi.conv_fwd(x, w, nbr, ld, n, mask=mask), args.iters)
+        t2, _ = timed(lambda: abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1, c_out=args.cin, mask=mask),
+                      args.iters)
+        print(f"T={T_} B={B_} I={I_}: fwd {t:.3f} ms dgrad {t2:.3f} ms path={abi.last_path()}", flush=True)
+    if args.sweep:
+        for k_ in ("MK_TC_T", "MK_TC_BSTAGES", "MK_TC_ISLOTS"):
+            os.environ.pop(k_, None)
     if "fwd" in what:
         t, _ = timed(lambda: abi.conv_fwd(x, w, nbr, ld, n, mask=mask), args.iters)
         print(f"fwd   {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  path={abi.last_path()}", flush=True)
