@@ -164,6 +164,7 @@ def run_engine(args):
     import MinkowskiEngine as ME
     import MinkowskiEngineBackend._C as _C
     from mink_octtree_stablediffusion_b200 import _lib
+    from mink_octtree_stablediffusion_b200.parallel import allreduce_gradients
     lib = _lib.load(build_if_missing=False)        # fail loudly if the CUDA library is missing
     dev = torch.device("cuda", local)
     pk = peaks()
@@ -266,7 +267,7 @@ def run_engine(args):
         o = conv(s)                                  # kernel-map build + forward
         o.F.backward(dy)                             # dgrad + wgrad
         if world > 1:
-            dist.all_reduce(conv.kernel.grad)
+            allreduce_gradients([conv.kernel])       # the only exchange of the data-parallel step
         grad_hs[slot].copy_(conv.kernel.grad, non_blocking=True)
         chk_hs[slot].copy_(o.F.detach()[:1024].float().sum().view(1), non_blocking=True)   # detached: the host
         # buffer must not keep the step's autograd graph (and its maps / tables) alive
