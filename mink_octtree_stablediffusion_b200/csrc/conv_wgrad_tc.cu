@@ -30,6 +30,7 @@
 //   warp  17    MMA issuer
 //   warp  18    dy tile loader (TMA)
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -63,6 +64,7 @@ struct Params {
   int a_stages, b_bufs;
   int ntiles, X;
   uint32_t idesc;
+  int knock;   // development aid (MK_WG_KNOCK): 1 = no gather copies, 2 = no MMA
 };
 
 struct Ring {
@@ -78,22 +80,39 @@ __device__ __forceinline__ uint32_t mask_bit(const uint32_t (&w)[4], int k) {
   return (word >> (k & 31)) & 1u;
 }
 
-// per-tile view of this CTA's pairs: bit u of `pairs` = pair j0+u has work;
-// bits 2u / 2u+1 of `panels` = its first / second panel is real and non-empty
-struct TileSched { uint32_t pairs, panels; };
+// Lane u of every role warp keeps the constants of the CTA's unit u (computed
+// once, with the divisions): the offsets / channel panels of its two panels.
+struct UnitConst {
+  int k0, k1, pi0, pi1;   // k1 == K: the second panel does not exist
+  bool valid;
+};
+__device__ __forceinline__ UnitConst unit_const(const Params &p, int j0, int npair_cta, int lane) {
+  UnitConst c;
+  const int q0 = 2 * (j0 + lane);
+  c.k0 = q0 / p.pa; c.pi0 = q0 % p.pa;
+  c.k1 = (q0 + 1) / p.pa; c.pi1 = (q0 + 1) % p.pa;
+  c.valid = lane < npair_cta;
+  if (c.k1 >= p.K) c.k1 = p.K;
+  return c;
+}
 
-__device__ __forceinline__ TileSched tile_sched(const Params &p, int tile, int j0, int npair_cta) {
-  uint32_t w[4] = {0u, 0u, 0u, 0u};
-  for (int i = 0; i < p.W; ++i) w[i] = __ldg(p.mask + (int64_t)tile * p.W + i);
-  TileSched s{0u, 0u};
-  for (int u = 0; u < npair_cta; ++u) {
-    const int q0 = 2 * (j0 + u);
-    const int k0 = q0 / p.pa, k1 = (q0 + 1) / p.pa;
-    const uint32_t b0 = mask_bit(w, k0);
-    const uint32_t b1 = k1 < p.K ? mask_bit(w, k1) : 0u;
-    s.pairs |= (b0 | b1) << u;
-    s.panels |= (b0 << (2 * u)) | (b1 << (2 * u + 1));
-  }
+// per-tile view of this CTA's units: bit u of `pairs` = unit u has work; bit u of
+// `p0` / `p1` = its first / second panel is real and non-empty.  Whole (converged)
+// warp; a few instructions (the role warps run it once per tile on their critical path).
+struct TileSched { uint32_t pairs, p0, p1; };
+
+__device__ __forceinline__ void load_mask(const Params &p, int tile, uint32_t (&w)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) w[i] = (i < p.W && tile < p.ntiles) ? __ldg(p.mask + (int64_t)tile * p.W + i) : 0u;
+}
+
+__device__ __forceinline__ TileSched tile_sched(const Params &p, const uint32_t (&w)[4], const UnitConst &c) {
+  const uint32_t b0 = c.valid ? mask_bit(w, c.k0) : 0u;
+  const uint32_t b1 = (c.valid && c.k1 < p.K) ? mask_bit(w, c.k1) : 0u;
+  TileSched s;
+  s.p0 = __ballot_sync(0xffffffffu, b0 != 0u);
+  s.p1 = __ballot_sync(0xffffffffu, b1 != 0u);
+  s.pairs = s.p0 | s.p1;
   return s;
 }
 }  // namespace wg
@@ -152,15 +171,20 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const int row0 = 32 * q + 8 * rsub;
     Ring ir, ar;
     uint32_t e = 0;
+    const UnitConst uc = unit_const(p, j0, npair_cta, lane);
+    uint32_t wn[4];
+    load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
-      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
+      load_mask(p, tile + p.X, wn);   // next tile's mask: its latency hides behind this tile
+      const TileSched ts = tile_sched(p, w, uc);
       for (int u = 0; u < npair_cta; ++u) {
         if (!((ts.pairs >> u) & 1u)) continue;
+        const int pi0 = __shfl_sync(0xffffffffu, uc.pi0, u), pi1 = __shfl_sync(0xffffffffu, uc.pi1, u);
         for (int hf = 0; hf < 2; ++hf, ++e) {
-          const bool real = (ts.panels >> (2 * u + hf)) & 1u;
+          const bool real = ((hf ? ts.p1 : ts.p0) >> u) & 1u;
           if ((e & (kGatherTeams - 1)) == team) {
-            const int qq = 2 * (j0 + u) + hf;
-            const int pi = qq % p.pa;
+            const int pi = hf ? pi1 : pi0;
             const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
             const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
             int4 i0 = make_int4(-1, -1, -1, -1), i1 = i0;
@@ -176,6 +200,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
             const uint32_t sb =
                 a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)row0 * 128u;
             const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+            if (!(p.knock & 1))
 #pragma unroll
             for (int i = 0; i < 8; ++i)
               cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
@@ -221,12 +246,19 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     // ===================== neighbour-index prefetch =====================
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
+    const UnitConst uc = unit_const(p, j0, npair_cta, lane);
+    uint32_t wn[4];
+    load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
-      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
+      load_mask(p, tile + p.X, wn);
+      const TileSched ts = tile_sched(p, w, uc);
       for (int u = 0; u < npair_cta; ++u) {
+        if (!((ts.pairs >> u) & 1u)) continue;
+        const int k0 = __shfl_sync(0xffffffffu, uc.k0, u), k1 = __shfl_sync(0xffffffffu, uc.k1, u);
         for (int hf = 0; hf < 2; ++hf) {
-          if (!((ts.panels >> (2 * u + hf)) & 1u)) continue;
-          const int k = (2 * (j0 + u) + hf) / p.pa;
+          if (!(((hf ? ts.p1 : ts.p0) >> u) & 1u)) continue;
+          const int k = hf ? k1 : k0;
           mbar_wait_warp(&i_empty[ir.stage], ir.phase ^ 1u);
           if (lane == 0) {
             const int32_t *src = p.nbr + (int64_t)k * p.ld + (int64_t)tile * kTileM;
@@ -246,8 +278,13 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const uint64_t desc0 = smem_desc_sw128(0, kPanelBytes, 1024);
     Ring ar, br;
     uint32_t inited = 0;
+    const UnitConst uc = unit_const(p, j0, npair_cta, lane);
+    uint32_t wn[4];
+    load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
-      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
+      load_mask(p, tile + p.X, wn);
+      const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
       mbar_wait_warp(&b_full[br.stage], br.phase);
       const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
@@ -260,6 +297,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
           const uint32_t d = tmem_base + (uint32_t)(u * p.nbpad);
           const uint64_t ad0 = desc0 | (uint64_t)(((a_base + ar.stage * kStageBytes) & 0x3FFFFu) >> 4);
           uint32_t acc = (inited >> u) & 1u;
+          if (!(p.knock & 2))
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             umma_f16(d, ad0 + (uint64_t)(ks * 128), bd0 + (uint64_t)(ks * 128), p.idesc, acc);
@@ -286,8 +324,13 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     // ===================== dy tile loader (TMA) =====================
     const uint32_t b_base = smem_u32(b_ring);
     Ring br;
+    const UnitConst uc = unit_const(p, j0, npair_cta, lane);
+    uint32_t wn[4];
+    load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
-      const TileSched ts = tile_sched(p, tile, j0, npair_cta);
+      const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
+      load_mask(p, tile + p.X, wn);
+      const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
       mbar_wait_warp(&b_empty[br.stage], br.phase ^ 1u);
       if (lane == 0) {
@@ -426,6 +469,7 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, 
   p.a_stages = pl.a_stages; p.b_bufs = pl.b_bufs;
   p.ntiles = pl.ntiles; p.X = pl.X;
   p.idesc = idesc_f16(dtype == MK_BF16 ? 1 : 0, kTileM, pl.NB, 1, 1);
+  p.knock = getenv("MK_WG_KNOCK") ? atoi(getenv("MK_WG_KNOCK")) : 0;
   { int rc = arm_hang_report(); if (rc) return rc; }
   static bool attr_set = false;
   if (!attr_set) {

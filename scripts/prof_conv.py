@@ -33,6 +33,24 @@ def offsets3():
     return np.array([[x, y, z] for z in r for y in r for x in r], np.int32)
 
 
+def reorder(c, how):
+    """Host-side experiment: the row order the engine's tile ordering would produce."""
+    M = 1 << 11
+    key = (c[:, 1].astype(np.int64) * M + c[:, 2]) * M + c[:, 3]
+    srt = np.argsort(key)
+    ks = key[srt]
+    pat = np.zeros(len(c), np.uint64)
+    for k, (dx, dy, dz) in enumerate(offsets3()):
+        q = key + (int(dx) * M + int(dy)) * M + int(dz)
+        i = np.clip(np.searchsorted(ks, q), 0, len(c) - 1)
+        pat |= (ks[i] == q).astype(np.uint64) << np.uint64(k)
+    if how == "pattern":
+        return c[np.argsort(pat, kind="stable")]
+    b = int(how[1:])
+    blk = ((c[:, 1] >> b).astype(np.int64) * M + (c[:, 2] >> b)) * M + (c[:, 3] >> b)
+    return c[np.lexsort((pat, blk))]
+
+
 def timed(fn, iters):
     ts = []
     for _ in range(iters):
@@ -55,6 +73,7 @@ def main():
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--shuffle", type=int, default=0, help="1: random row order instead of sorted")
     ap.add_argument("--dense", type=int, default=0, help="S: dense SxSxS cube instead of the sphere surface")
+    ap.add_argument("--order", default="", help="bN: rows sorted by (2^N block, neighbour pattern); morton; pattern (experiment)")
     ap.add_argument("--sweep", default="", help="semicolon list of T,BSTAGES,ISLOTS settings of the conv kernel (dev knobs)")
     args = ap.parse_args()
     what = set(args.what.split(","))
@@ -67,6 +86,8 @@ def main():
         c = sphere(args.r)
     if args.shuffle:
         c = c[np.random.default_rng(1).permutation(len(c))]
+    if args.order:
+        c = reorder(c, args.order)
     n = len(c)
     offs = offsets3()
     t_ins, tin = timed(lambda: abi.insert(c), args.iters if "insert" in what else 1)
