@@ -48,6 +48,14 @@ unsigned int *hang_report_device_ptr() {
   return g_hang_dev;
 }
 
+}  // namespace mk
+// development aid: the watchdog's last report {magic, block, warp, (smem addr << 1) | parity}
+extern "C" int mk_debug_hang_words(unsigned int *out4) {
+  if (!mk::g_hang_host) return 1;
+  for (int i = 0; i < 4; ++i) out4[i] = mk::g_hang_host[i];
+  return 0;
+}
+namespace mk {
 int cuda_fail(cudaError_t e, const char *what) {
   if (g_hang_host && g_hang_host[0] == 0xDEADBA44u)
     set_error("CUDA error %d (%s) at %s; pipeline wait timed out in block (%u,%u) warp %u on mbarrier smem 0x%x parity %u",
