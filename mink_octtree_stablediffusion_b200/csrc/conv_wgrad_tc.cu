@@ -72,6 +72,10 @@ struct Ring {
   __device__ __forceinline__ void advance(uint32_t n) {
     if (++stage == n) { stage = 0; phase ^= 1u; }
   }
+  __device__ __forceinline__ void skip(uint32_t by, uint32_t n) {   // by <= n
+    stage += by;
+    if (stage >= n) { stage -= n; phase ^= 1u; }
+  }
 };
 
 // bit k of a tile's mask words (W <= 4)
@@ -244,6 +248,9 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     tc_fence_before();
   } else if (warp == kWarpIdx) {
     // ===================== neighbour-index prefetch =====================
+    // Lane i moves the tile's i-th real panel: its own slot, its own wait, its own
+    // 512-byte bulk copy, so the per-panel barrier latency is paid once per tile
+    // instead of once per panel (a tile has up to 2 * kMaxUnits = kIdxSlots panels).
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
     const UnitConst uc = unit_const(p, j0, npair_cta, lane);
@@ -253,22 +260,24 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
       load_mask(p, tile + p.X, wn);
       const TileSched ts = tile_sched(p, w, uc);
-      for (int u = 0; u < npair_cta; ++u) {
-        if (!((ts.pairs >> u) & 1u)) continue;
-        const int k0 = __shfl_sync(0xffffffffu, uc.k0, u), k1 = __shfl_sync(0xffffffffu, uc.k1, u);
-        for (int hf = 0; hf < 2; ++hf) {
-          if (!(((hf ? ts.p1 : ts.p0) >> u) & 1u)) continue;
-          const int k = hf ? k1 : k0;
-          mbar_wait_warp(&i_empty[ir.stage], ir.phase ^ 1u);
-          if (lane == 0) {
-            const int32_t *src = p.nbr + (int64_t)k * p.ld + (int64_t)tile * kTileM;
-            mbar_arrive_expect_tx(&i_full[ir.stage], kTileM * 4);
-            bulk_g2s(i_base + ir.stage * (kTileM * 4), src, kTileM * 4, &i_full[ir.stage]);
-          }
-          __syncwarp();
-          ir.advance(kIdxSlots);
-        }
+      // panel q = 2u + hf is real iff bit q of pm
+      uint32_t pm = 0;
+      for (int u = 0; u < npair_cta; ++u) pm |= (((ts.p0 >> u) & 1u) << (2 * u)) | (((ts.p1 >> u) & 1u) << (2 * u + 1));
+      const uint32_t n = (uint32_t)__popc(pm);
+      const bool act = (uint32_t)lane < n;
+      const uint32_t q = act ? __fns(pm, 0, lane + 1) : 0u;
+      const int k0 = __shfl_sync(0xffffffffu, uc.k0, (int)(q >> 1)), k1 = __shfl_sync(0xffffffffu, uc.k1, (int)(q >> 1));
+      if (act) {
+        const int k = (q & 1u) ? k1 : k0;
+        uint32_t slot = ir.stage + (uint32_t)lane, ph = ir.phase;
+        if (slot >= (uint32_t)kIdxSlots) { slot -= kIdxSlots; ph ^= 1u; }
+        mbar_wait(&i_empty[slot], ph ^ 1u);
+        const int32_t *src = p.nbr + (int64_t)k * p.ld + (int64_t)tile * kTileM;
+        mbar_arrive_expect_tx(&i_full[slot], kTileM * 4);
+        bulk_g2s(i_base + slot * (kTileM * 4), src, kTileM * 4, &i_full[slot]);
       }
+      __syncwarp();
+      ir.skip(n, kIdxSlots);
     }
   } else if (warp == kWarpMma) {
     // ===================== MMA issuer =====================

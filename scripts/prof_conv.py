@@ -52,15 +52,17 @@ def reorder(c, how):
 
 
 def timed(fn, iters):
-    ts = []
+    """Mean device time of `iters` back-to-back calls after one warm-up (the queue stays
+    full, so the host-side cost of a call does not show up as device idle time)."""
+    out = fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
     for _ in range(iters):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
         out = fn()
-        b.record()
-        torch.cuda.synchronize()
-        ts.append(a.elapsed_time(b))
-    return float(np.median(ts)), out
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters, out
 
 
 def main():
