@@ -40,6 +40,22 @@ namespace mk {
 using namespace sm100;
 
 namespace wg {
+// -DMK_TC_PROF: per-CTA cycle counters of where each role waits (development aid;
+// read back with mk_debug_wg_prof_read).  Compiled out of the product build.
+#ifdef MK_TC_PROF
+__device__ unsigned long long g_wprof[256 * 32];
+#define WP_DECL(...) unsigned long long __VA_ARGS__
+#define WP_T0(v) v = clock64()
+#define WP_ADD(acc, t0) acc += clock64() - (t0)
+#define WP_ELAPSED(v) v = clock64() - (v)
+#define WP_PUT(slot, v) g_wprof[(blockIdx.y * gridDim.x + blockIdx.x) * 32 + (slot)] = (v)
+#else
+#define WP_DECL(...)
+#define WP_T0(v)
+#define WP_ADD(acc, t0)
+#define WP_ELAPSED(v)
+#define WP_PUT(slot, v)
+#endif
 constexpr int kTileM = 128;
 constexpr int kPanelBytes = kTileM * 128;   // [128 rows x 64 ch] 16-bit
 constexpr int kStageBytes = 2 * kPanelBytes;
@@ -175,32 +191,43 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const int row0 = 32 * q + 8 * rsub;
     Ring ir, ar;
     uint32_t e = 0;
+    WP_DECL(g_wi = 0, g_wa = 0, g_is = 0, g_t0 = 0, g_start = 0, g_blk = 0, g_b0 = 0, g_sch = 0, g_s0 = 0;)
+    WP_T0(g_start);
     const UnitConst uc = unit_const(p, j0, npair_cta, lane);
     uint32_t wn[4];
     load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
+      WP_T0(g_s0);
       const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
       load_mask(p, tile + p.X, wn);   // next tile's mask: its latency hides behind this tile
       const TileSched ts = tile_sched(p, w, uc);
+      WP_ADD(g_sch, g_s0);
       for (int u = 0; u < npair_cta; ++u) {
         if (!((ts.pairs >> u) & 1u)) continue;
-        const int pi0 = __shfl_sync(0xffffffffu, uc.pi0, u), pi1 = __shfl_sync(0xffffffffu, uc.pi1, u);
+        int pi0 = 0, pi1 = 0;
+        if (p.pa > 1) { pi0 = __shfl_sync(0xffffffffu, uc.pi0, u); pi1 = __shfl_sync(0xffffffffu, uc.pi1, u); }
         for (int hf = 0; hf < 2; ++hf, ++e) {
           const bool real = ((hf ? ts.p1 : ts.p0) >> u) & 1u;
           if ((e & (kGatherTeams - 1)) == team) {
+            WP_T0(g_b0);
             const int pi = hf ? pi1 : pi0;
             const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
             const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
             int4 i0 = make_int4(-1, -1, -1, -1), i1 = i0;
             if (real) {
+              WP_T0(g_t0);
               mbar_wait_warp(&i_full[ir.stage], ir.phase);
+              WP_ADD(g_wi, g_t0);
               const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + ir.stage * kTileM + row0);
               i0 = ip[0];
               i1 = ip[1];
               __syncwarp();
               if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
             }
+            WP_T0(g_t0);
             mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
+            WP_ADD(g_wa, g_t0);
+            WP_T0(g_t0);
             const uint32_t sb =
                 a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)row0 * 128u;
             const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
@@ -210,11 +237,18 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
               cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
                          xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
             cp_async_arrive_noinc(&a_full[ar.stage]);
+            WP_ADD(g_is, g_t0);
+            WP_ADD(g_blk, g_b0);
           }
           if (real) ir.advance(kIdxSlots);
         }
         ar.advance(S);
       }
+    }
+    if (lane == 0 && (warp & 3) == 0) {
+      WP_PUT(8 + 4 * team, g_wi); WP_PUT(9 + 4 * team, g_wa); WP_PUT(10 + 4 * team, g_is);
+      if (team == 0) { WP_PUT(4, g_blk); WP_PUT(5, g_sch); }
+      WP_ELAPSED(g_start); WP_PUT(11 + 4 * team, g_start);
     }
     if (warp >= 4) goto done_role;   // only warps 0-3 (TMEM lane quarters) run the epilogue
     // ===================== epilogue: TMEM -> fp32 partial =====================
@@ -287,6 +321,8 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const uint64_t desc0 = smem_desc_sw128(0, kPanelBytes, 1024);
     Ring ar, br;
     uint32_t inited = 0;
+    WP_DECL(m_wb = 0, m_wa = 0, m_is = 0, m_t0 = 0, m_start = 0, m_n = 0;)
+    WP_T0(m_start);
     const UnitConst uc = unit_const(p, j0, npair_cta, lane);
     uint32_t wn[4];
     load_mask(p, xs, wn);
@@ -295,11 +331,16 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       load_mask(p, tile + p.X, wn);
       const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
+      WP_T0(m_t0);
       mbar_wait_warp(&b_full[br.stage], br.phase);
+      WP_ADD(m_wb, m_t0);
       const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
       for (int u = 0; u < npair_cta; ++u) {
         if (!((ts.pairs >> u) & 1u)) continue;
+        WP_T0(m_t0);
         mbar_wait_warp(&a_full[ar.stage], ar.phase);
+        WP_ADD(m_wa, m_t0);
+        WP_T0(m_t0);
         fence_proxy_async_smem();
         tc_fence_after();
         if (elect_one()) {
@@ -315,12 +356,17 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
           umma_commit(&a_empty[ar.stage]);
         }
         __syncwarp();
+        WP_ADD(m_is, m_t0);
         inited |= 1u << u;
         ar.advance(S);
       }
       if (elect_one()) umma_commit(&b_empty[br.stage]);
       __syncwarp();
       br.advance(NBUF);
+    }
+    if (lane == 0) {
+      WP_PUT(0, m_wb); WP_PUT(1, m_wa); WP_PUT(2, m_is);
+      WP_ELAPSED(m_start); WP_PUT(3, m_start);
     }
     if (lane == 0) { *inited_slot = inited; __threadfence_block(); }
     __syncwarp();
@@ -499,3 +545,9 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, 
 }
 
 }  // namespace mk
+
+#ifdef MK_TC_PROF
+extern "C" int mk_debug_wg_prof_read(unsigned long long *host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, mk::wg::g_wprof, sizeof(unsigned long long) * n);
+}
+#endif

@@ -1,0 +1,47 @@
+"""Role wait-time counters of k_conv_wgrad_tc (library built with -DMK_TC_PROF).
+
+    MK_NVCC_EXTRA=-DMK_TC_PROF python -m mink_octtree_stablediffusion_b200.build && python scripts/wg_prof.py
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "scripts"))
+import abi  # noqa: E402
+from prof_conv import offsets3, sphere  # noqa: E402
+from mink_octtree_stablediffusion_b200 import _lib  # noqa: E402
+
+lib = _lib.load()
+c = sphere(271)
+n = len(c)
+tin = abi.insert(c)
+nbr, ld, counts = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offsets3())
+x = torch.randn(n, 64).bfloat16().cuda()
+dy = torch.randn(n, 64).bfloat16().cuda()
+mask = abi.tile_mask(nbr, n, ld, 27)
+names = {0: "mma wait b_full", 1: "mma wait a_full", 2: "mma issue", 3: "mma loop total", 4: "team0 in-panel block", 5: "team0 tile sched"}
+for t in range(4):
+    names.update({8 + 4 * t: f"team{t} wait i_full", 9 + 4 * t: f"team{t} wait a_empty", 10 + 4 * t: f"team{t} issue",
+                  11 + 4 * t: f"team{t} loop total"})
+for kn in sys.argv[1:] or ["0"]:
+    os.environ["MK_WG_KNOCK"] = kn
+    for _ in range(3):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        abi.conv_wgrad(x, dy, nbr, ld, n, 27, mask=mask)
+        b.record()
+        torch.cuda.synchronize()
+    buf = np.zeros(148 * 32, np.uint64)
+    lib.mk_debug_wg_prof_read.argtypes = [C.c_void_p, C.c_int]
+    assert lib.mk_debug_wg_prof_read(buf.ctypes.data_as(C.c_void_p), len(buf)) == 0
+    buf = buf.reshape(148, 32).astype(np.float64)
+    print(f"== knock={kn}: {a.elapsed_time(b):.3f} ms; mean over CTAs (kcycles)")
+    for k in sorted(names):
+        v = buf[:, k]
+        print(f"  {names[k]:22s} {v.mean() / 1e3:10.1f}  (min {v.min() / 1e3:.1f} max {v.max() / 1e3:.1f})")
