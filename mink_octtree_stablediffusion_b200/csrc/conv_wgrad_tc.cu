@@ -88,9 +88,9 @@ struct Ring {
   __device__ __forceinline__ void advance(uint32_t n) {
     if (++stage == n) { stage = 0; phase ^= 1u; }
   }
-  __device__ __forceinline__ void skip(uint32_t by, uint32_t n) {   // by <= n
+  __device__ __forceinline__ void skip(uint32_t by, uint32_t n) {
     stage += by;
-    if (stage >= n) { stage -= n; phase ^= 1u; }
+    while (stage >= n) { stage -= n; phase ^= 1u; }
   }
 };
 
@@ -190,7 +190,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const int c16 = lane & 7, rsub = lane >> 3;
     const int row0 = 32 * q + 8 * rsub;
     Ring ir, ar;
-    uint32_t e = 0;
+    uint32_t nstage = 0;                           // stages so far
     WP_DECL(g_wi = 0, g_wa = 0, g_is = 0, g_t0 = 0, g_start = 0, g_blk = 0, g_b0 = 0, g_sch = 0, g_s0 = 0;)
     WP_T0(g_start);
     const UnitConst uc = unit_const(p, j0, npair_cta, lane);
@@ -202,48 +202,59 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       load_mask(p, tile + p.X, wn);   // next tile's mask: its latency hides behind this tile
       const TileSched ts = tile_sched(p, w, uc);
       WP_ADD(g_sch, g_s0);
-      for (int u = 0; u < npair_cta; ++u) {
-        if (!((ts.pairs >> u) & 1u)) continue;
-        int pi0 = 0, pi1 = 0;
-        if (p.pa > 1) { pi0 = __shfl_sync(0xffffffffu, uc.pi0, u); pi1 = __shfl_sync(0xffffffffu, uc.pi1, u); }
-        for (int hf = 0; hf < 2; ++hf, ++e) {
-          const bool real = ((hf ? ts.p1 : ts.p0) >> u) & 1u;
-          if ((e & (kGatherTeams - 1)) == team) {
-            WP_T0(g_b0);
-            const int pi = hf ? pi1 : pi0;
-            const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
-            const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
-            int4 i0 = make_int4(-1, -1, -1, -1), i1 = i0;
-            if (real) {
-              WP_T0(g_t0);
-              mbar_wait_warp(&i_full[ir.stage], ir.phase);
-              WP_ADD(g_wi, g_t0);
-              const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + ir.stage * kTileM + row0);
-              i0 = ip[0];
-              i1 = ip[1];
-              __syncwarp();
-              if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
-            }
-            WP_T0(g_t0);
-            mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
-            WP_ADD(g_wa, g_t0);
-            WP_T0(g_t0);
-            const uint32_t sb =
-                a_base + ar.stage * kStageBytes + (uint32_t)hf * kPanelBytes + (uint32_t)row0 * 128u;
-            const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
-            if (!(p.knock & 1))
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-              cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
-                         xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
-            cp_async_arrive_noinc(&a_full[ar.stage]);
-            WP_ADD(g_is, g_t0);
-            WP_ADD(g_blk, g_b0);
-          }
-          if (real) ir.advance(kIdxSlots);
+      // Panel e = 2 * (stage number) + hf goes to team e & 3: a team owns half hf =
+      // team & 1 of every second stage, so it walks the set bits of `pairs` and acts
+      // on the stages of its parity only; the ring positions of a stage / of a real
+      // panel follow from bit counts, nothing is advanced panel by panel.
+      const uint32_t hf = team & 1u;
+      const uint32_t real_mask = hf ? ts.p1 : ts.p0;
+      uint32_t rank = 0;
+      for (uint32_t b = ts.pairs; b; b &= b - 1u, ++rank) {
+        if (((nstage + rank) & 1u) != (team >> 1)) continue;
+        const int u = __ffs((int)b) - 1;
+        const uint32_t below = (1u << u) - 1u;
+        const bool real = (real_mask >> u) & 1u;
+        WP_T0(g_b0);
+        int pi = 0;
+        if (p.pa > 1) pi = __shfl_sync(0xffffffffu, hf ? uc.pi1 : uc.pi0, u);
+        const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
+        const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
+        Ring as = ar;
+        as.skip(rank, S);
+        int4 i0 = make_int4(-1, -1, -1, -1), i1 = i0;
+        if (real) {
+          // real panels before this one: both halves of the pairs below u, and the first half of u
+          Ring is = ir;
+          is.skip((uint32_t)__popc(ts.p0 & below) + (uint32_t)__popc(ts.p1 & below) + (hf ? ((ts.p0 >> u) & 1u) : 0u),
+                  kIdxSlots);
+          WP_T0(g_t0);
+          mbar_wait_warp(&i_full[is.stage], is.phase);
+          WP_ADD(g_wi, g_t0);
+          const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + is.stage * kTileM + row0);
+          i0 = ip[0];
+          i1 = ip[1];
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&i_empty[is.stage]);
         }
-        ar.advance(S);
+        WP_T0(g_t0);
+        mbar_wait_warp(&a_empty[as.stage], as.phase ^ 1u);
+        WP_ADD(g_wa, g_t0);
+        WP_T0(g_t0);
+        const uint32_t sb = a_base + as.stage * kStageBytes + hf * kPanelBytes + (uint32_t)row0 * 128u;
+        const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+        if (!(p.knock & 1))
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
+                     xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
+        cp_async_arrive_noinc(&a_full[as.stage]);
+        WP_ADD(g_is, g_t0);
+        WP_ADD(g_blk, g_b0);
       }
+      const uint32_t n_st = (uint32_t)__popc(ts.pairs);
+      nstage += n_st;
+      ar.skip(n_st, S);
+      ir.skip((uint32_t)__popc(ts.p0) + (uint32_t)__popc(ts.p1), kIdxSlots);
     }
     if (lane == 0 && (warp & 3) == 0) {
       WP_PUT(8 + 4 * team, g_wi); WP_PUT(9 + 4 * team, g_wa); WP_PUT(10 + 4 * team, g_is);
