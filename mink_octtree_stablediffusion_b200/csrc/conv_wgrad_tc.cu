@@ -23,12 +23,12 @@
 // each CTA writes its fp32 partial to the workspace and a second kernel sums
 // the X partials in a fixed order.
 //
-// CTA roles (608 threads, 1 CTA / SM):
+// CTA roles (640 threads, 1 CTA / SM):
 //   warps 0-15  gather producers (four teams of four warps, one panel per team
 //               at a time); warps 0-3 then run the epilogue (TMEM -> fp32 partial)
 //   warp  16    neighbour-index prefetch (bulk copies into a smem ring)
-//   warp  17    MMA issuer
-//   warp  18    dy tile loader (TMA)
+//   warps 17-18 MMA issuers (unit u of the CTA -> warp u mod 2)
+//   warp  19    dy tile loader (TMA)
 #include <algorithm>
 #include <cstdlib>
 
@@ -61,8 +61,9 @@ constexpr int kPanelBytes = kTileM * 128;   // [128 rows x 64 ch] 16-bit
 constexpr int kStageBytes = 2 * kPanelBytes;
 constexpr int kGatherTeams = 4;
 constexpr int kGatherWarps = 4 * kGatherTeams;   // a team of 4 warps fills one panel (32 rows per warp)
-constexpr int kWarpIdx = kGatherWarps, kWarpMma = kGatherWarps + 1, kWarpDy = kGatherWarps + 2;
-constexpr int kThreads = 32 * (kGatherWarps + 3);
+constexpr int kMmaWarps = 2;   // MMA warp m issues for the CTA's units u = m (mod 2): accumulators nobody else touches
+constexpr int kWarpIdx = kGatherWarps, kWarpMma = kGatherWarps + 1, kWarpDy = kWarpMma + kMmaWarps;
+constexpr int kThreads = 32 * (kGatherWarps + 2 + kMmaWarps);
 constexpr int kIdxSlots = 32;
 constexpr int kMaxUnits = 16;
 
@@ -149,10 +150,14 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
   int32_t *idx_ring = (int32_t *)(b_ring + (size_t)NBUF * b_bytes);
   uint64_t *bars = (uint64_t *)(idx_ring + kIdxSlots * kTileM);
   uint64_t *a_full = bars, *a_empty = a_full + S;
-  uint64_t *b_full = a_empty + S, *b_empty = b_full + NBUF;
-  uint64_t *i_full = b_empty + NBUF, *i_empty = i_full + kIdxSlots;
-  uint64_t *done = i_empty + kIdxSlots;
-  uint32_t *tmem_slot = (uint32_t *)(done + 1);
+  // b_empty / done: one barrier per MMA warp.  Two tcgen05.commit from different warps
+  // onto ONE mbarrier were seen to lose an arrival when they come close together
+  // (the kernel hung with the MMAs knocked out, i.e. back-to-back commits), so
+  // every barrier here has a single committing thread.
+  uint64_t *b_full = a_empty + S, *b_empty = b_full + NBUF;             // b_empty[buf * kMmaWarps + m]
+  uint64_t *i_full = b_empty + NBUF * kMmaWarps, *i_empty = i_full + kIdxSlots;
+  uint64_t *done = i_empty + kIdxSlots;                                 // done[m]
+  uint32_t *tmem_slot = (uint32_t *)(done + kMmaWarps);
   uint32_t *inited_slot = tmem_slot + 1;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -162,10 +167,11 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
   const int xs = blockIdx.x;
 
   if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 256); mbar_init(&a_empty[s], 1); }
-    for (uint32_t s = 0; s < NBUF; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 256); mbar_init(&a_empty[s], kMmaWarps); }
+    for (uint32_t s = 0; s < NBUF; ++s) mbar_init(&b_full[s], 1);
+    for (uint32_t s = 0; s < NBUF * kMmaWarps; ++s) mbar_init(&b_empty[s], 1);
     for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], 4); }
-    mbar_init(done, 1);
+    for (int m = 0; m < kMmaWarps; ++m) mbar_init(&done[m], 2);
     *inited_slot = 0u;
     fence_barrier_init();
   }
@@ -263,7 +269,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     }
     if (warp >= 4) goto done_role;   // only warps 0-3 (TMEM lane quarters) run the epilogue
     // ===================== epilogue: TMEM -> fp32 partial =====================
-    mbar_wait_warp(done, 0u);
+    for (int m = 0; m < kMmaWarps; ++m) mbar_wait_warp(&done[m], 0u);
     tc_fence_after();
     const uint32_t inited = *(volatile uint32_t *)inited_slot;
     float *part = p.partial + (size_t)xs * p.K * p.c_in * p.c_out;
@@ -324,17 +330,26 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       __syncwarp();
       ir.skip(n, kIdxSlots);
     }
-  } else if (warp == kWarpMma) {
-    // ===================== MMA issuer =====================
+  } else if (warp >= kWarpMma && warp < kWarpMma + kMmaWarps) {
+    // ===================== MMA issuers =====================
+    // The serial cost of a stage on the issuing warp (barrier wait, proxy fence,
+    // eight blocking UMMA issues, commit: ~600 cycles, measured) exceeds the ~390
+    // cycles the stage keeps the tensor pipe busy, so one warp cannot keep the pipe
+    // fed.  The CTA's units are independent accumulators: two warps share them by
+    // unit parity, each walks the set bits of the tile's schedule and touches only
+    // the A stages of its own units.  On the dy buffers, shared by both, every warp
+    // waits and arrives once per tile.
+    const uint32_t mw = (uint32_t)(warp - kWarpMma);
     const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_ring);
     // MN-major SW128 operands: LBO = distance between 64-channel panels,
     // SBO = 1024 B between 8-row groups; 16 rows (one MMA) = 2048 B
     const uint64_t desc0 = smem_desc_sw128(0, kPanelBytes, 1024);
     Ring ar, br;
     uint32_t inited = 0;
-    WP_DECL(m_wb = 0, m_wa = 0, m_is = 0, m_t0 = 0, m_start = 0, m_n = 0;)
+    WP_DECL(m_wb = 0, m_wa = 0, m_is = 0, m_t0 = 0, m_start = 0;)
     WP_T0(m_start);
     const UnitConst uc = unit_const(p, j0, npair_cta, lane);
+    const uint32_t mine_mask = 0x55555555u << mw;   // kMmaWarps == 2
     uint32_t wn[4];
     load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
@@ -343,20 +358,32 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
       WP_T0(m_t0);
-      mbar_wait_warp(&b_full[br.stage], br.phase);
+      mbar_wait_shared(&b_full[br.stage], br.phase);   // kMmaWarps waiters
+      __syncwarp();
       WP_ADD(m_wb, m_t0);
       const uint64_t bd0 = desc0 | (uint64_t)(((b_base + br.stage * b_bytes) & 0x3FFFFu) >> 4);
-      for (int u = 0; u < npair_cta; ++u) {
-        if (!((ts.pairs >> u) & 1u)) continue;
+      Ring as = ar;
+      for (uint32_t b = ts.pairs; b; b &= b - 1u, as.advance(S)) {
+        const int u = __ffs((int)b) - 1;
+        // Every warp waits on every stage, also on the other warp's, and the slot is
+        // released by both (the owner's commit + the other's plain arrive): a parity
+        // wait is only sound for a waiter that sees each phase of its barrier - one
+        // that skips uses, or is not part of the release, can be two phases out.
         WP_T0(m_t0);
-        mbar_wait_warp(&a_full[ar.stage], ar.phase);
+        mbar_wait_shared(&a_full[as.stage], as.phase);
+        __syncwarp();
         WP_ADD(m_wa, m_t0);
+        if (!((mine_mask >> u) & 1u)) {
+          if (lane == 0) mbar_arrive(&a_empty[as.stage]);
+          __syncwarp();
+          continue;
+        }
         WP_T0(m_t0);
         fence_proxy_async_smem();
         tc_fence_after();
         if (elect_one()) {
           const uint32_t d = tmem_base + (uint32_t)(u * p.nbpad);
-          const uint64_t ad0 = desc0 | (uint64_t)(((a_base + ar.stage * kStageBytes) & 0x3FFFFu) >> 4);
+          const uint64_t ad0 = desc0 | (uint64_t)(((a_base + as.stage * kStageBytes) & 0x3FFFFu) >> 4);
           uint32_t acc = (inited >> u) & 1u;
           if (!(p.knock & 2))
 #pragma unroll
@@ -364,27 +391,27 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
             umma_f16(d, ad0 + (uint64_t)(ks * 128), bd0 + (uint64_t)(ks * 128), p.idesc, acc);
             acc = 1u;
           }
-          umma_commit(&a_empty[ar.stage]);
+          umma_commit(&a_empty[as.stage]);
         }
         __syncwarp();
         WP_ADD(m_is, m_t0);
         inited |= 1u << u;
-        ar.advance(S);
       }
-      if (elect_one()) umma_commit(&b_empty[br.stage]);
+      ar.skip((uint32_t)__popc(ts.pairs), S);
+      if (elect_one()) umma_commit(&b_empty[br.stage * kMmaWarps + mw]);
       __syncwarp();
       br.advance(NBUF);
     }
-    if (lane == 0) {
+    if (lane == 0 && mw == 0) {
       WP_PUT(0, m_wb); WP_PUT(1, m_wa); WP_PUT(2, m_is);
       WP_ELAPSED(m_start); WP_PUT(3, m_start);
     }
-    if (lane == 0) { *inited_slot = inited; __threadfence_block(); }
-    __syncwarp();
-    if (elect_one()) {
-      if (inited) umma_commit(done);
-      else mbar_arrive(done);
+    if (lane == 0) {
+      atomicOr(inited_slot, inited);
+      mbar_arrive(&done[mw]);                  // release: orders the flag before the phase completes
     }
+    __syncwarp();
+    if (elect_one()) umma_commit(&done[mw]);   // ... and the warp's MMAs
     __syncwarp();
   } else {
     // ===================== dy tile loader (TMA) =====================
@@ -398,7 +425,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       load_mask(p, tile + p.X, wn);
       const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
-      mbar_wait_warp(&b_empty[br.stage], br.phase ^ 1u);
+      for (int m = 0; m < kMmaWarps; ++m) mbar_wait_warp(&b_empty[br.stage * kMmaWarps + m], br.phase ^ 1u);
       if (lane == 0) {
         mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
         for (int pn = 0; pn < p.pb; ++pn)
@@ -484,6 +511,13 @@ bool make_wplan(int dtype, int64_t n_out, int K, int c_in, int c_out, WPlan &pl)
   if (fixed + 2 * b_tile + 2 * (size_t)kStageBytes > budget) pl.b_bufs = 1;
   if (fixed + pl.b_bufs * b_tile + 2 * (size_t)kStageBytes > budget) return false;
   pl.a_stages = (int)std::min<size_t>(6, (budget - fixed - pl.b_bufs * b_tile) / kStageBytes);
+  // A gather team owns the stages of one parity (of the running stage number).  With an
+  // even ring the same teams refill a given slot every time, so a team sees every
+  // phase of the a_empty barriers it waits on whatever the order the two MMA warps
+  // release the slots in (with an odd ring it would see every other phase: unsound).
+  pl.a_stages &= ~1;
+  if (pl.a_stages < 2) return false;
+  if (fixed + 3 * b_tile + (size_t)pl.a_stages * kStageBytes <= budget && pl.b_bufs == 2) pl.b_bufs = 3;
   pl.smem = fixed + pl.b_bufs * b_tile + (size_t)pl.a_stages * kStageBytes;
   pl.partial_bytes = align256w((size_t)pl.X * K * c_in * c_out * 4);
   pl.mask_bytes = align256w((size_t)pl.ntiles * pl.W * 4);

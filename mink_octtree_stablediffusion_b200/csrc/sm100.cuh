@@ -54,6 +54,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// try_wait without a suspend-time hint (the hardware's own short time limit): for
+// barriers that several warps wait on at once.  The hinted form sleeps on the
+// barrier (NANOSLEEP.SYNCS); with two warps asleep on one barrier a phase
+// completion was seen to wake only one, the other slept out its 10 ms hint
+// (measured on the dy-tile barrier of the weight-gradient kernel).
+__device__ __forceinline__ bool mbar_try_wait_short(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Bounded wait: a pipeline bug must surface as an error (trap -> sticky CUDA
 // error, reported by the next API call), never as a hung GPU.  The report goes
 // to a word of mapped host memory (it survives the dead context); everything is
@@ -69,6 +85,30 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int bu
       if (t0 == 0) {
         t0 = now;
       } else if (now - t0 > 10000000000LL * budget) {  // ~5 s
+        unsigned int *h = mk_hang_slot;
+        if (h) {
+          h[1] = blockIdx.x | (blockIdx.y << 16);
+          h[2] = threadIdx.x >> 5;
+          h[3] = (smem_u32(bar) << 1) | parity;
+          h[0] = 0xDEADBA44u;
+          __threadfence_system();
+        }
+        asm volatile("trap;");
+      }
+    }
+  }
+}
+
+// multi-waiter wait: short polls, same watchdog
+__device__ __forceinline__ void mbar_wait_shared(uint64_t *bar, uint32_t parity, int budget = 1) {
+  uint32_t spins = 0;
+  long long t0 = 0;
+  while (!mbar_try_wait_short(bar, parity)) {
+    if ((++spins & 0xFFFFu) == 0) {
+      const long long now = clock64();
+      if (t0 == 0) {
+        t0 = now;
+      } else if (now - t0 > 10000000000LL * budget) {
         unsigned int *h = mk_hang_slot;
         if (h) {
           h[1] = blockIdx.x | (blockIdx.y << 16);
