@@ -140,3 +140,61 @@ def test_conv_linearity_and_zero_rows_large():
     # the three inner products cancel heavily (|a| ~ sqrt(N)); compare on the scale of the summands
     scale = float(dy.double().norm() * y1.double().norm())
     assert abs(a - b) <= 1e-5 * scale and abs(a - cc) <= 1e-5 * scale
+
+
+def _northstar_cloud(R, order):
+    """Sphere-surface cloud in one of the row orders the engine must not care about."""
+    c = O.sphere_surface(R, seed=0)
+    if order == "shuffled":
+        c = c[np.random.default_rng(3).permutation(len(c))]
+    elif order == "blocks":      # rows grouped by 32^3 block: tiles whose rows share few offsets
+        key = ((c[:, 1] >> 5).astype(np.int64) << 40) | ((c[:, 2] >> 5).astype(np.int64) << 20) | (c[:, 3] >> 5)
+        c = c[np.argsort(key, kind="stable")]
+    return np.ascontiguousarray(c.astype(np.int32))
+
+
+@pytest.mark.parametrize("R,order", [(271, "sorted"), (120, "shuffled"), (120, "blocks")])
+def test_tensor_core_path_at_scale(R, order):
+    """The tcgen05 kernels at the north-star size (1 M voxels, 3^3, 64 -> 64, bf16), where the
+    oracle is too slow: (1) agreement with the engine's own fp32 CUDA-core path on the same
+    bf16-rounded inputs, (2) bit-identical results from run to run (no atomics, fixed reduction
+    order), (3) adjointness <dy, conv(x)> = <dgrad(dy), x> = <wgrad(x, dy), W>."""
+    c = _northstar_cloud(R, order)
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(n, 64, generator=g).bfloat16().cuda()
+    dy = torch.randn(n, 64, generator=g).bfloat16().cuda()
+    w = (torch.randn(27, 64, 64, generator=g) / 40).bfloat16().cuda()
+
+    def run():
+        y = abi.conv_fwd(x, w, nbr, ld, n)
+        assert abi.last_path() == 1, "tensor-core path expected"
+        gi = abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1)
+        gw = abi.conv_wgrad(x, dy, nbr, ld, n, 27)
+        assert abi.last_path() == 1
+        return y, gi, gw
+
+    y, gi, gw = run()
+    y2, gi2, gw2 = run()
+    assert torch.equal(y, y2) and torch.equal(gi, gi2) and torch.equal(gw, gw2)
+    # fp32 CUDA-core path on the same values
+    abi.force_simt(1)
+    try:
+        xf, dyf, wf = x.float(), dy.float(), w.float()
+        y_s = abi.conv_fwd(xf, wf, nbr, ld, n)
+        gi_s = abi.conv_fwd(dyf, wf, nbr, ld, n, transpose_w=1, kflip=1)
+        gw_s = abi.conv_wgrad(xf, dyf, nbr, ld, n, 27)
+        assert abi.last_path() == 0
+    finally:
+        abi.force_simt(0)
+    for got, ref in ((y, y_s), (gi, gi_s), (gw, gw_s)):
+        err = float((got.float() - ref).abs().max() / ref.abs().max())
+        assert err <= 1e-2, err
+    a = float((dy.double() * y_s.double()).sum())
+    b = float((gi_s.double() * x.double()).sum())
+    cc = float((gw_s.double() * w.double()).sum())
+    scale = float(dy.double().norm() * y_s.double().norm())
+    assert abs(a - b) <= 1e-5 * scale and abs(a - cc) <= 1e-5 * scale
