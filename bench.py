@@ -327,10 +327,10 @@ def run_engine(args):
     stage = {}
     if rank == 0:
         from mink_octtree_stablediffusion_b200 import backend_ops as _ops
-        ins, kmb, kme = [], [], []
+        ins, kmb, kme, kto = [], [], [], []
         busy = torch.empty((8192, 8192), dtype=torch.bfloat16, device=dev).normal_()
         for _ in range(7):
-            a, b, c2, d2 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+            a, b, c2, d2, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(5))
             m2 = _C.CoordinateMapManagerGPU_c10()
             torch.mm(busy, busy)     # ~1 ms of device work: the host runs ahead, the events time the device only
             a.record()
@@ -344,13 +344,18 @@ def run_engine(args):
             m2.kernel_map(k2, k2, kg.kernel_size, kg.kernel_stride, kg.kernel_dilation, kg.region_type, empty_off,
                           False, False)
             d2.record()
+            # ... and the tile-ordered form the tensor-core kernels read (sort by block + neighbour pattern,
+            # permuted table, tile mask); built once per kernel map, on its first 16-bit convolution
+            _ops._ordered(m2, next(iter(m2._kmaps.values())))
+            e2.record()
             torch.cuda.synchronize()
             ins.append(a.elapsed_time(b))
             kmb.append(b.elapsed_time(c2))
             kme.append(c2.elapsed_time(d2))
+            kto.append(d2.elapsed_time(e2))
         K = KS ** 3
         stage = {"hash_insert_ms": float(np.median(ins)), "kmap_build_ms": float(np.median(kmb)),
-                 "kmap_pairs_export_ms": float(np.median(kme)),
+                 "kmap_pairs_export_ms": float(np.median(kme)), "kmap_tile_order_ms": float(np.median(kto)),
                  "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n)}
 
     # ---- reduce over ranks -----------------------------------------------------

@@ -163,6 +163,23 @@ int64_t mk_kmap_tile_mask_words(int K);
 int mk_kmap_tile_mask(const int32_t *nbr, int64_t n_rows, int64_t ld, int K,
                       uint32_t *mask, void *stream);
 
+/* Tile ordering (an internal layout of the engine, no counterpart in the
+ * reference: ME's gather-GEMM-scatter works on per-offset pair lists).  The
+ * tensor-core kernels process 128 table columns at a time and skip an offset
+ * only when none of the 128 rows has a neighbour under it.  `order` [n_rows]
+ * is a permutation of the table's columns sorted by (batch, 2^block_log2
+ * block of the row's coordinate, neighbour pattern), nbr_ordered [K, ld] the
+ * same table with column s = old column order[s] (padding -1).  Row indices
+ * INSIDE the table are untouched.  coords may be NULL (pattern only).  The
+ * coordinate map's row order does not change: mk_conv_fwd_rows writes row
+ * order[s]; for the weight gradient the caller gathers dy through `order`
+ * (mk_rows_gather) and calls mk_conv_wgrad on the ordered table. */
+int64_t mk_kmap_tile_order_workspace_bytes(int64_t n_rows);
+int mk_kmap_tile_order(const int32_t *nbr, int64_t n_rows, int64_t ld, int K,
+                       const int32_t *coords, int ncols, int block_log2,
+                       int32_t *order, int32_t *nbr_ordered, void *workspace,
+                       void *stream);
+
 /* ------------------------------------------------------------------------
  * Convolution.  Replaces ConvolutionForwardGPU / ConvolutionBackwardGPU and
  * the Transpose variants (extern.hpp:84-114,151-181): the matmul / matmul2
@@ -189,6 +206,17 @@ int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
                 int64_t ld, int64_t n_out, int64_t n_in,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream);
+/* 1 if the tcgen05 kernels (forward and weight gradient) serve this shape. */
+int mk_conv_tc_eligible(int dtype, int64_t n_rows, int K, int c_in, int c_out);
+/* mk_conv_fwd on a tile-ordered table (mk_kmap_tile_order): column o of the
+ * table is output row out_rows[o], i.e. y[out_rows[o], :] = sum_k ...  Served
+ * by the tensor-core path only (MK_EUNSUPPORTED otherwise); out_rows == NULL
+ * is mk_conv_fwd. */
+int mk_conv_fwd_rows(int dtype, const void *x, const void *w, int transpose_w,
+                     int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                     int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                     int c_out, void *y, const int32_t *out_rows,
+                     void *workspace, void *stream);
 /* dW[k] = sum_o x[nbr[k,o], :]^T  dy[o, :]    dW: [K, Cin, Cout] (dtype) */
 int mk_conv_wgrad(int dtype, const void *x, const void *dy,
                   const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,

@@ -231,7 +231,8 @@ class _CoordMap:
 
 class _KernelMap:
     """Output-stationary neighbour table + lazily derived forms."""
-    __slots__ = ("nbr", "ld", "n_in", "n_out", "K", "counts", "_inv", "_pairs", "symmetric", "_mask", "_imask")
+    __slots__ = ("nbr", "ld", "n_in", "n_out", "K", "counts", "_inv", "_pairs", "symmetric", "_mask", "_imask",
+                 "out_coords", "in_coords", "_ordered", "_iordered")
 
     def __init__(self, nbr, ld, n_in, n_out, K, counts, symmetric):
         self.nbr, self.ld, self.n_in, self.n_out, self.K = nbr, ld, n_in, n_out, K
@@ -241,6 +242,10 @@ class _KernelMap:
         self._mask = None             # tile masks of nbr / of the inverse table (lazy)
         self._imask = None
         self.symmetric = symmetric    # inverse table == table with offsets mirrored
+        self.out_coords = None        # coordinates of the table's columns / of the inverse table's columns
+        self.in_coords = None
+        self._ordered = None          # tile-ordered forms (order, table, mask), lazy: see backend_ops._ordered
+        self._iordered = None
 
 
 def _pad_ld(n: int) -> int:

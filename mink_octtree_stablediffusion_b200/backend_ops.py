@@ -27,7 +27,9 @@ def _build_table(mgr, out_map: _CoordMap, in_map: _CoordMap, offsets: np.ndarray
     # per-offset pair counts are not needed by the table form (the CSR export counts on its own)
     _lib.check(mgr._lib.mk_kmap_build(_ptr(out_map.coords), out_map.n, out_map.coords.shape[1], _ptr(in_map.table),
                                       in_map.capacity, _np_ptr(offs_h), K, _ptr(nbr), ld, None, _stream()))
-    return _KernelMap(nbr, ld, in_map.n, out_map.n, K, None, symmetric)
+    km = _KernelMap(nbr, ld, in_map.n, out_map.n, K, None, symmetric)
+    km.out_coords, km.in_coords = out_map.coords, in_map.coords
+    return km
 
 
 def _inverse_table(mgr, km: _KernelMap):
@@ -69,6 +71,52 @@ def _inv_mask(mgr, km: _KernelMap) -> torch.Tensor:
         inv, ld_in, _ = _inverse_table(mgr, km)
         km._imask = _tile_mask(mgr, inv, km.n_in, ld_in, km.K)
     return km._imask
+
+
+# Tile ordering (mk_kmap_tile_order): an internal column order of the table for the
+# tensor-core kernels.  MK_TILE_ORDER=0 switches it off, MK_TILE_ORDER_MIN is the
+# smallest table it is built for (below that the sort costs more than it saves),
+# MK_TILE_ORDER_BLOCK the log2 of the locality block.
+def _tile_order_cfg():
+    import os
+    return (os.environ.get("MK_TILE_ORDER", "1") != "0", int(os.environ.get("MK_TILE_ORDER_MIN", "65536")),
+            int(os.environ.get("MK_TILE_ORDER_BLOCK", "7")))
+
+
+def _order_table(mgr, table, n_rows, ld, K, coords):
+    lib = mgr._lib
+    dev = table.device
+    order = torch.empty(max(n_rows, 1), dtype=torch.int32, device=dev)
+    out = torch.empty((K, ld), dtype=torch.int32, device=dev)
+    ws = torch.empty(int(lib.mk_kmap_tile_order_workspace_bytes(n_rows)), dtype=torch.uint8, device=dev)
+    _lib.check(lib.mk_kmap_tile_order(_ptr(table), n_rows, ld, K, _ptr(coords), 0 if coords is None else coords.shape[1],
+                                      _tile_order_cfg()[2], _ptr(order), _ptr(out), _ptr(ws), _stream()))
+    return order, out, _tile_mask(mgr, out, n_rows, ld, K)
+
+
+def _want_order(mgr, x, n_rows, K, c_in, c_out) -> bool:
+    on, n_min, _ = _tile_order_cfg()
+    return (on and n_rows >= n_min and x.dtype in (torch.bfloat16, torch.float16)
+            and bool(mgr._lib.mk_conv_tc_eligible(_dtype_code(x), n_rows, K, c_in, c_out)))
+
+
+def _ordered(mgr, km: _KernelMap):
+    """(order, table, mask) of the forward table in tile order."""
+    if km._ordered is None:
+        km._ordered = _order_table(mgr, km.nbr, km.n_out, km.ld, km.K, km.out_coords)
+    return km._ordered
+
+
+def _inv_ordered(mgr, km: _KernelMap):
+    """Tile-ordered inverse table: (order, table, mask, ld, kflip)."""
+    if km.symmetric:
+        o, t, m = _ordered(mgr, km)
+        return o, t, m, km.ld, 1
+    if km._iordered is None:
+        inv, ld_in, _ = _inverse_table(mgr, km)
+        km._iordered = _order_table(mgr, inv, km.n_in, ld_in, km.K, km.in_coords)
+    o, t, m = km._iordered
+    return o, t, m, km._inv[1], 0
 
 
 def _pairs(mgr, km: _KernelMap):
@@ -174,16 +222,17 @@ def _workspace(lib, dtype_code, n, K, c_in, c_out, dev):
     return torch.empty(nbytes, dtype=torch.uint8, device=dev)
 
 
-def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in, c_out):
+def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in, c_out, order=None):
+    """y[o] = sum_k x[table[k, o]] @ W[k] (W[k]^T when transpose_w); with `order` the
+    table is tile-ordered and its column s is output row order[s]."""
     lib = mgr._lib
     y = torch.empty((n_rows, c_out), dtype=x.dtype, device=x.device)
     if n_rows == 0:
         return y
     code = _dtype_code(x)
     ws = _workspace(lib, code, n_rows, K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_fwd(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld, n_rows,
-                               x.size(0), K,
-                               c_in, c_out, _ptr(y), _ptr(ws), _stream()))
+    _lib.check(lib.mk_conv_fwd_rows(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld,
+                                    n_rows, x.size(0), K, c_in, c_out, _ptr(y), _ptr(order), _ptr(ws), _stream()))
     return y
 
 
@@ -192,10 +241,27 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
     dw = torch.empty((km.K, c_in, c_out), dtype=x.dtype, device=x.device)
     code = _dtype_code(x)
     ws = _workspace(lib, code, km.n_out, km.K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(km.nbr), _ptr(_fwd_mask(mgr, km)), km.ld, km.n_out, x.size(0), km.K, c_in,
-                                 c_out,
-                                 _ptr(dw), _ptr(ws), _stream()))
+    table, mask = km.nbr, None
+    if km.n_out > 0 and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
+        # the ordered table pairs column s with dy row order[s]
+        order, table, mask = _ordered(mgr, km)
+        dy_o = torch.empty_like(dy)
+        _lib.check(lib.mk_rows_gather(_ptr(dy), _ptr(order), km.n_out, dy.size(1) * dy.element_size(), _ptr(dy_o),
+                                      _stream()))
+        dy = dy_o
+    if mask is None:
+        mask = _fwd_mask(mgr, km)
+    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(table), _ptr(mask), km.ld, km.n_out, x.size(0), km.K,
+                                 c_in, c_out, _ptr(dw), _ptr(ws), _stream()))
     return dw
+
+
+def _conv_forward(mgr, x, w, km: _KernelMap):
+    c_in, c_out = w.size(1), w.size(2)
+    if km.n_out > 0 and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
+        order, table, mask = _ordered(mgr, km)
+        return _conv_apply(mgr, x, w, 0, 0, table, mask, km.ld, km.n_out, km.K, c_in, c_out, order)
+    return _conv_apply(mgr, x, w, 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K, c_in, c_out)
 
 
 def _resolve_out_key(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
@@ -231,8 +297,7 @@ def ConvolutionForwardGPU(in_feat, kernel, kernel_size, kernel_stride, kernel_di
     km = _kernel_map(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
                      False, False)
     _require(kernel.size(0) == km.K, "kernel.size(0) == kernel_volume")
-    return _conv_apply(mgr, in_feat, kernel.contiguous(), 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K,
-                       kernel.size(1), kernel.size(2))
+    return _conv_forward(mgr, in_feat, kernel.contiguous(), km)
 
 
 def _conv_backward(in_feat, grad_out, kernel, km, mgr):
@@ -241,10 +306,15 @@ def _conv_backward(in_feat, grad_out, kernel, km, mgr):
     _require(grad_out.size(1) == kernel.size(2), "grad_out_feat.size(1) == kernel.size(2)")
     _require(grad_out.dtype == in_feat.dtype, "grad_out_feat.scalar_type() == in_feat.scalar_type()")
     kernel = kernel.contiguous()
-    inv, ld_in, kflip = _inverse_table(mgr, km)
     # grad_in[i] = sum_k grad_out[inv[k, i]] @ W[k]^T
-    grad_in = _conv_apply(mgr, grad_out, kernel, 1, kflip, inv, _inv_mask(mgr, km), ld_in, km.n_in, km.K,
-                          kernel.size(2), kernel.size(1))
+    if km.n_in > 0 and _want_order(mgr, grad_out, km.n_in, km.K, kernel.size(2), kernel.size(1)):
+        order, inv, imask, ld_in, kflip = _inv_ordered(mgr, km)
+        grad_in = _conv_apply(mgr, grad_out, kernel, 1, kflip, inv, imask, ld_in, km.n_in, km.K,
+                              kernel.size(2), kernel.size(1), order)
+    else:
+        inv, ld_in, kflip = _inverse_table(mgr, km)
+        grad_in = _conv_apply(mgr, grad_out, kernel, 1, kflip, inv, _inv_mask(mgr, km), ld_in, km.n_in, km.K,
+                              kernel.size(2), kernel.size(1))
     grad_w = _conv_wgrad(mgr, in_feat, grad_out, km, kernel.size(1), kernel.size(2))
     return grad_in, grad_w
 
@@ -267,8 +337,7 @@ def ConvolutionTransposeForwardGPU(in_feat, kernel, kernel_size, kernel_stride, 
     km = _kernel_map(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
                      True, False)
     _require(kernel.size(0) == km.K, "kernel.size(0) == kernel_volume")
-    return _conv_apply(mgr, in_feat, kernel.contiguous(), 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K,
-                       kernel.size(1), kernel.size(2))
+    return _conv_forward(mgr, in_feat, kernel.contiguous(), km)
 
 
 def ConvolutionTransposeBackwardGPU(in_feat, grad_out_feat, kernel, kernel_size, kernel_stride, kernel_dilation,

@@ -18,7 +18,8 @@ int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w,
                 int kflip, const int32_t *nbr, const uint32_t *tile_mask,
                 int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
-                int c_out, void *y, void *workspace, cudaStream_t st);
+                int c_out, void *y, const int32_t *out_rows, void *workspace,
+                cudaStream_t st);
 // conv_wgrad_tc.cu
 bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
 int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
@@ -67,11 +68,30 @@ static int check_conv_args(int64_t ld, int64_t n_out, int K, int c_in,
   return MK_OK;
 }
 
+int mk_conv_tc_eligible(int dtype, int64_t n_rows, int K, int c_in,
+                        int c_out) {
+  return (!g_force_simt && n_rows > 0 &&
+          conv_fwd_tc_eligible(dtype, n_rows, K, c_in, c_out) &&
+          conv_wgrad_tc_eligible(dtype, n_rows, K, c_in, c_out))
+             ? 1
+             : 0;
+}
+
 int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
                 int kflip, const int32_t *nbr, const uint32_t *tile_mask,
                 int64_t ld, int64_t n_out, int64_t n_in,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream) {
+  return mk_conv_fwd_rows(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
+                          n_out, n_in, K, c_in, c_out, y, nullptr, workspace,
+                          stream);
+}
+
+int mk_conv_fwd_rows(int dtype, const void *x, const void *w, int transpose_w,
+                     int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                     int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                     int c_out, void *y, const int32_t *out_rows,
+                     void *workspace, void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
   if (rc) return rc;
   MK_CHECK_ARG(n_in >= 0, "n_in must be >= 0");
@@ -82,7 +102,12 @@ int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
       conv_fwd_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
     return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
-                       n_out, n_in, K, c_in, c_out, y, workspace, st);
+                       n_out, n_in, K, c_in, c_out, y, out_rows, workspace, st);
+  }
+  if (out_rows) {
+    set_error("mk_conv_fwd_rows: an output-row permutation is only served by "
+              "the tensor-core path (ask mk_conv_tc_eligible first)");
+    return MK_EUNSUPPORTED;
   }
   g_last_path = 0;
   return conv_fwd_simt_dispatch(dtype, x, w, transpose_w, kflip, nbr, ld,

@@ -78,6 +78,7 @@ struct ConvTCParams {
   const int32_t *nbr;     // [K, ld]
   const uint32_t *mask;   // [ntiles, W]
   void *y;                // [n_out, c_out]
+  const int32_t *out_rows; // optional [n_out]: table column o is output row out_rows[o] (tile-ordered maps)
   int64_t ld, n_out, n_in;
   int K, W, kflip;
   int c_in, c_out, nchunk, NT, T;
@@ -249,8 +250,9 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         if (tile >= ntiles) break;
         uint32_t touched = 0;
         for (int wi = 0; wi < p.W; ++wi) touched |= __ldg(p.mask + tile * p.W + wi);
-        const int64_t row = tile * kTileM + warp * 32 + lane;
-        T *yrow = (T *)p.y + (size_t)row * p.c_out + (size_t)sp * p.NT;
+        const int64_t row = tile * kTileM + warp * 32 + lane;   // table column
+        const int64_t orow = (p.out_rows && row < p.n_out) ? (int64_t)__ldg(p.out_rows + row) : row;
+        T *yrow = (T *)p.y + (size_t)orow * p.c_out + (size_t)sp * p.NT;
         const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * 256 + t * acc_stride);
         for (int c0 = 0; c0 < p.NT; c0 += 16) {
           uint32_t v[16];
@@ -597,7 +599,8 @@ int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint
 template <typename T>
 static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const void *w, int transpose_w, int kflip,
                              const int32_t *nbr, const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in,
-                             int K, int c_in, int c_out, void *y, void *workspace, cudaStream_t st) {
+                             int K, int c_in, int c_out, void *y, const int32_t *out_rows, void *workspace,
+                             cudaStream_t st) {
   uint8_t *ws = (uint8_t *)workspace;
   T *bpack = (T *)ws;
   uint32_t *mask = (uint32_t *)(ws + pl.bpack_bytes);
@@ -615,7 +618,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   }
   ConvTCParams p;
   p.x = x;
-  p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y;
+  p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y; p.out_rows = out_rows;
   p.ld = ld; p.n_out = n_out; p.n_in = n_in; p.K = K; p.W = pl.W; p.kflip = kflip;
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
   p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots;
@@ -644,7 +647,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
 
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
                 const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
-                void *y, void *workspace, cudaStream_t st) {
+                void *y, const int32_t *out_rows, void *workspace, cudaStream_t st) {
   TCPlan pl;
   if (!make_plan(dtype, n_out, K, c_in, c_out, pl)) {
     set_error("conv_fwd_tc: shape not eligible");
@@ -652,9 +655,9 @@ int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kf
   }
   if (dtype == MK_BF16)
     return conv_fwd_tc_typed<__nv_bfloat16>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K,
-                                            c_in, c_out, y, workspace, st);
+                                            c_in, c_out, y, out_rows, workspace, st);
   return conv_fwd_tc_typed<__half>(pl, 0, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, c_in, c_out,
-                                   y, workspace, st);
+                                   y, out_rows, workspace, st);
 }
 
 // weight gradient on tensor cores: conv_wgrad_tc.cu

@@ -100,6 +100,37 @@ def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None, mask=None
     return y
 
 
+def tile_order(nbr, n_rows, ld, K, coords_dev=None, block_log2=7):
+    """(order [n_rows], table in tile order [K, ld])"""
+    lib = _lib.load()
+    order = torch.empty(max(n_rows, 1), dtype=torch.int32, device="cuda")
+    out = torch.empty((K, ld), dtype=torch.int32, device="cuda")
+    ws = torch.empty(int(lib.mk_kmap_tile_order_workspace_bytes(n_rows)), dtype=torch.uint8, device="cuda")
+    _lib.check(lib.mk_kmap_tile_order(P(nbr), n_rows, ld, K, P(coords_dev), 0 if coords_dev is None else coords_dev.shape[1],
+                                      block_log2, P(order), P(out), P(ws), S()))
+    return order[:n_rows], out
+
+
+def conv_fwd_rows(x, w, nbr, ld, n_out, out_rows, transpose_w=0, kflip=0, mask=None):
+    lib = _lib.load()
+    K = w.shape[0]
+    c_in = x.shape[1]
+    c_out = w.shape[1] if transpose_w else w.shape[2]
+    y = torch.empty((n_out, c_out), dtype=x.dtype, device="cuda")
+    ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
+                     device="cuda")
+    _lib.check(lib.mk_conv_fwd_rows(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0],
+                                    K, c_in, c_out, P(y), P(out_rows), P(ws), S()))
+    return y
+
+
+def rows_gather(src, idx):
+    lib = _lib.load()
+    dst = torch.empty((idx.numel(), src.shape[1]), dtype=src.dtype, device="cuda")
+    _lib.check(lib.mk_rows_gather(P(src), P(idx), idx.numel(), src.shape[1] * src.element_size(), P(dst), S()))
+    return dst
+
+
 def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None):
     lib = _lib.load()
     c_in, c_out = x.shape[1], dy.shape[1]

@@ -198,3 +198,43 @@ def test_tensor_core_path_at_scale(R, order):
     cc = float((gw_s.double() * w.double()).sum())
     scale = float(dy.double().norm() * y_s.double().norm())
     assert abs(a - b) <= 1e-5 * scale and abs(a - cc) <= 1e-5 * scale
+
+
+@pytest.mark.parametrize("R,order,with_coords", [(60, "sorted", True), (60, "shuffled", True), (40, "sorted", False)])
+def test_tile_ordered_table(R, order, with_coords):
+    """mk_kmap_tile_order: `order` is a permutation, the ordered table is the table with its
+    columns permuted (bit-exact), it touches fewer (tile, offset) pairs, and the convolution on
+    it (mk_conv_fwd_rows / dy gathered for the weight gradient) gives the same result: the
+    forward bit-identical (a row's accumulation sequence does not depend on its tile), the
+    weight gradient within the bf16 tolerance (the voxel reduction is re-associated)."""
+    c = _northstar_cloud(R, order)
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    perm, nbr_t = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"] if with_coords else None)
+    ph = perm.cpu().numpy()
+    assert np.array_equal(np.sort(ph), np.arange(n))
+    nh, th = nbr.cpu().numpy(), nbr_t.cpu().numpy()
+    assert np.array_equal(th[:, :n], nh[:, ph]) and (th[:, n:] == -1).all()
+    m0 = abi.tile_mask(nbr, n, ld, 27).cpu().numpy().view(np.uint32)
+    m1 = abi.tile_mask(nbr_t, n, ld, 27).cpu().numpy().view(np.uint32)
+    popc = lambda m: int(np.unpackbits(m.view(np.uint8)).sum())
+    assert popc(m1) <= popc(m0)
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(n, 64, generator=g).bfloat16().cuda()
+    dy = torch.randn(n, 64, generator=g).bfloat16().cuda()
+    w = (torch.randn(27, 64, 64, generator=g) / 40).bfloat16().cuda()
+    y0 = abi.conv_fwd(x, w, nbr, ld, n)
+    y1 = abi.conv_fwd_rows(x, w, nbr_t, ld, n, perm)
+    assert abi.last_path() == 1
+    assert torch.equal(y0, y1)
+    g0 = abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1)
+    g1 = abi.conv_fwd_rows(dy, w, nbr_t, ld, n, perm, transpose_w=1, kflip=1)
+    assert torch.equal(g0, g1)
+    w0 = abi.conv_wgrad(x, dy, nbr, ld, n, 27)
+    w1 = abi.conv_wgrad(x, abi.rows_gather(dy, perm), nbr_t, ld, n, 27)
+    assert float((w0.float() - w1.float()).abs().max() / w0.float().abs().max()) <= 1e-2
+    # fp32 has no tensor-core path: an output permutation must be refused, not ignored
+    with pytest.raises(RuntimeError):
+        abi.conv_fwd_rows(x.float(), w.float(), nbr_t, ld, n, perm)
