@@ -376,7 +376,7 @@ def run_engine(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": "north_star_conv_1M_k3_c64", "voxels_per_gpu": n, "pairs_per_gpu": P,
                        "generator": f"sphere surface R={R}", "kernel": "3x3x3 stride 1", "channels": "64->64",
-                       "step": "conv fwd + dgrad + wgrad, kernel map cached", "parallelism": f"dp{world}",
+                       "step": "conv fwd + dgrad + wgrad, kernel map (table + tile-ordered form) cached", "parallelism": f"dp{world}",
                        "l2": "working set (features, grads, neighbour table ~0.7 GB) exceeds the 126 MB L2"},
             "roofline": {"bound": "tensor", "kernel": "conv forward (%s)" % ("tcgen05" if conv_path else "simt"),
                          "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,

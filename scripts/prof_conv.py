@@ -51,6 +51,10 @@ def reorder(c, how):
     return c[np.lexsort((pat, blk))]
 
 
+def _popc(mask):
+    return np.unpackbits(mask.cpu().numpy().view(np.uint8)).sum()
+
+
 def timed(fn, iters):
     """Mean device time of `iters` back-to-back calls after one warm-up (the queue stays
     full, so the host-side cost of a call does not show up as device idle time)."""
@@ -76,6 +80,7 @@ def main():
     ap.add_argument("--shuffle", type=int, default=0, help="1: random row order instead of sorted")
     ap.add_argument("--dense", type=int, default=0, help="S: dense SxSxS cube instead of the sphere surface")
     ap.add_argument("--order", default="", help="bN: rows sorted by (2^N block, neighbour pattern); morton; pattern (experiment)")
+    ap.add_argument("--tile-order", type=int, default=0, help="1: run the conv kernels on the engine's tile-ordered table")
     ap.add_argument("--sweep", default="", help="semicolon list of T,BSTAGES,ISLOTS settings of the conv kernel (dev knobs)")
     args = ap.parse_args()
     what = set(args.what.split(","))
@@ -103,6 +108,17 @@ def main():
     w = (torch.randn(27, args.cin, args.cout, generator=g) / np.sqrt(27 * args.cin)).to(dt).cuda()
     mask = abi.tile_mask(nbr, n, ld, 27)
     fl = 2.0 * P * args.cin * args.cout
+    if args.tile_order:
+        t_to, (perm, nbr_o) = timed(lambda: abi.tile_order(nbr, n, ld, 27, tin["coords_dev"]), args.iters)
+        mask_o = abi.tile_mask(nbr_o, n, ld, 27)
+        print(f"tile order (+alloc) {t_to:.3f} ms; non-empty (tile, offset) pairs {int(_popc(mask))} -> {int(_popc(mask_o))}", flush=True)
+        t, _ = timed(lambda: abi.conv_fwd_rows(x, w, nbr_o, ld, n, perm, mask=mask_o), args.iters)
+        print(f"fwd   {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered)", flush=True)
+        t, _ = timed(lambda: abi.conv_fwd_rows(dy, w, nbr_o, ld, n, perm, transpose_w=1, kflip=1, mask=mask_o), args.iters)
+        print(f"dgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered)", flush=True)
+        t, _ = timed(lambda: abi.conv_wgrad(x, abi.rows_gather(dy, perm), nbr_o, ld, n, 27, mask=mask_o), args.iters)
+        print(f"wgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered, incl. dy gather)", flush=True)
+        return
     for cfg in [c_ for c_ in args.sweep.split(";") if c_]:
         T_, B_, I_ = cfg.split(",")
         os.environ["MK_TC_T"], os.environ["MK_TC_BSTAGES"], os.environ["MK_TC_ISLOTS"] = T_, B_, I_
