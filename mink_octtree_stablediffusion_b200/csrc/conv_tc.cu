@@ -240,7 +240,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
           for (int wi = 0; wi < p.W; ++wi) any |= __ldg(p.mask + (tile0 + t) * p.W + wi);
       if (any) {
         PROF_T0(pe_t0);
-        mbar_wait_warp(&t_full[h], (it >> 1) & 1u, 3);   // outermost wait: report inner stalls first
+        mbar_wait_warp(&t_full[h], (it >> 1) & 1u, 3, 400);   // outermost wait: report inner stalls first
         tc_fence_after();
         PROF_ADD(pe_wait, pe_t0);
       }
@@ -329,76 +329,112 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     // warp instruction).  Completion is tracked by the hardware
     // (cp.async.mbarrier.arrive.noinc); a team whose tile has no neighbour under
     // the offset just arrives; one extra arrive publishes the ticket.
+    // The loop is bound by instruction issue (16 warps x a few hundred instructions
+    // per stage, measured with ncu's source view), so everything that does not change
+    // is computed once, shared memory is addressed in its own space (a generic
+    // pointer costs generic LD/ST plus a cvta per barrier operation) and the
+    // schedule is walked on a register bit mask.
     const int gw = warp - kWarpGather0;
     const uint32_t team = (uint32_t)gw >> 2;
     const int q = gw & 3;
     uint8_t *sched = sched_all + (2 + gw) * kMaxK;
-    const uint32_t a_base = smem_u32(a_ring);
+    const uint32_t sched_s = smem_u32(sched);
     const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
     const int c16 = lane & 7, rsub = lane >> 3;
     const int row0 = 32 * q + 8 * rsub;            // first of this lane's 8 rows (multiple of 8)
     const uint32_t T = (uint32_t)p.T;
+    // lane-constant parts of the addresses.  Destination of instruction i: bits 4-6 =
+    // c16 ^ i (swizzle), bits 7-9 = i (row in the 8-row atom): both an XOR with i * 144,
+    // as the atom base has those bits clear.
+    const uint32_t dst_lane = smem_u32(a_ring) + (uint32_t)row0 * 128u + ((uint32_t)c16 << 4);
+    const uint32_t idx_lane = smem_u32(idx_ring) + (uint32_t)row0 * 4u;
+    const uint8_t *x_lane = (const uint8_t *)p.x + (size_t)c16 * 16;
+    const uint32_t b_a_full = smem_u32(a_full), b_a_empty = smem_u32(a_empty);
+    const uint32_t b_i_full = smem_u32(i_full), b_i_empty = smem_u32(i_empty);
+    const uint32_t tickets_s = smem_u32(tickets);
+    const bool ticket_lane = q == 0 && lane == 0;
+    const uint32_t nchunk = (uint32_t)p.nchunk;
     Ring ir, ar;                                   // idx slot of the row's first tile / current A stage
     uint32_t nst = 0;                              // stages so far
     uint32_t it = 0;                               // groups with work so far
     PROF_DECL(pg_we = 0, pg_wi = 0, pg_iss = 0, pg_t0 = 0, pg_n = 0;)
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
       const int64_t tile0 = (int64_t)g * p.T;
-      const uint32_t n_stages = fill_sched(sched, p, tile0, ntiles, lane) * (uint32_t)p.nchunk;
+      const uint32_t n_stages = fill_sched(sched, p, tile0, ntiles, lane) * nchunk;
       if (!n_stages) continue;
+      // offsets with work, as a bit mask in registers (sched[] itself is in shared memory)
+      uint32_t any0, any1 = 0, any2 = 0, any3 = 0;
+      any0 = __ballot_sync(0xffffffffu, lane < p.K && lds_u8(sched_s + (uint32_t)lane) != 0u);
+      if (p.K > 32) {
+        any1 = __ballot_sync(0xffffffffu, 32 + lane < p.K && lds_u8(sched_s + 32u + (uint32_t)lane) != 0u);
+        any2 = __ballot_sync(0xffffffffu, 64 + lane < p.K && lds_u8(sched_s + 64u + (uint32_t)lane) != 0u);
+        any3 = __ballot_sync(0xffffffffu, 96 + lane < p.K && lds_u8(sched_s + 96u + (uint32_t)lane) != 0u);
+      }
       const uint32_t tk_group = (it & 1u) << 8 | ((((it >> 1) & 1u) ^ 1u) ? kTkEmptyParity : 0u);
       uint32_t seen = 0, done = 0;                 // tiles already accumulated into / stages of the group so far
-      for (int k = 0; k < p.K; ++k) {
-        const uint32_t bits = sched[k];
-        if (!bits) continue;
-        for (int ch = 0; ch < p.nchunk; ++ch, ++nst, ++done) {
-          bool waited = false;
-          for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
-            if (!waited) {
+#pragma unroll 1
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll 1
+        for (uint32_t m = j == 0 ? any0 : j == 1 ? any1 : j == 2 ? any2 : any3; m; m &= m - 1u) {
+          const uint32_t k = 32u * (uint32_t)j + (uint32_t)__ffs((int)m) - 1u;
+          const uint32_t bits = lds_u8(sched_s + k);
+          const uint32_t i_full_k = b_i_full + ir.stage * 8u, i_empty_k = b_i_empty + ir.stage * 8u;
+          const uint32_t idx_k = idx_lane + ir.stage * (idx_slot * 4u);
+#pragma unroll 1
+          for (uint32_t ch = 0; ch < nchunk; ++ch, ++nst, ++done) {
+            const uint32_t a_full_s = b_a_full + ar.stage * 8u;
+            const uint32_t dst_s = dst_lane + ar.stage * stage_bytes;
+            bool waited = false;
+#pragma unroll 1
+            for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
+              if (!waited) {
+                PROF_T0(pg_t0);
+                mbar_wait_warp_a(b_a_empty + ar.stage * 8u, ar.phase ^ 1u);
+                PROF_ADD(pg_we, pg_t0);
+                waited = true;
+              }
+              if (t == 0 && ticket_lane) {
+                const uint32_t nks = kFull ? 4u : (uint32_t)min(4, (p.c_in - (int)ch * 64) >> 4);
+                uint32_t tk = tk_group | bits | ((ch > 0 ? 0xFu : seen) << 4) | (nks << 16);
+                if (done == 0) tk |= kTkGroupBegin;
+                if (done == n_stages - 1) tk |= kTkGroupEnd;
+                sts_u32(tickets_s + ar.stage * 4u, tk);
+                mbar_arrive_a(a_full_s);             // release: orders the ticket before the phase completes
+              }
+              if (!((bits >> t) & 1u)) {
+                mbar_arrive_a(a_full_s);             // nothing to gather: stand in for the cp.async arrivals
+                if (lane == 0) mbar_arrive_a(i_empty_k);
+                continue;
+              }
               PROF_T0(pg_t0);
-              mbar_wait_warp(&a_empty[ar.stage], ar.phase ^ 1u);
-              PROF_ADD(pg_we, pg_t0);
-              waited = true;
-            }
-            if (t == 0 && q == 0 && lane == 0) {
-              const uint32_t nks = kFull ? 4u : (uint32_t)min(4, (p.c_in - ch * 64) >> 4);
-              uint32_t tk = tk_group | bits | ((ch > 0 ? 0xFu : seen) << 4) | (nks << 16);
-              if (done == 0) tk |= kTkGroupBegin;
-              if (done == n_stages - 1) tk |= kTkGroupEnd;
-              tickets[ar.stage] = tk;
-              mbar_arrive(&a_full[ar.stage]);      // release: orders the ticket before the phase completes
-            }
-            if (!((bits >> t) & 1u)) {
-              mbar_arrive(&a_full[ar.stage]);      // nothing to gather: stand in for the cp.async arrivals
-              if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
-              continue;
-            }
-            PROF_T0(pg_t0);
-            mbar_wait_warp(&i_full[ir.stage], ir.phase);
-            PROF_ADD(pg_wi, pg_t0);
-            PROF_T0(pg_t0);
-            const int4 *ip =
-                reinterpret_cast<const int4 *>(idx_ring + ir.stage * idx_slot + t * kTileM + row0);
-            const int4 i0 = ip[0], i1 = ip[1];
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&i_empty[ir.stage]);
-            const uint32_t szok = (ch * 64 + c16 * 8) < p.c_in ? 16u : 0u;
-            const uint8_t *xb = (const uint8_t *)p.x + (size_t)ch * 128 + (size_t)c16 * 16;
-            const uint32_t sb = a_base + ar.stage * stage_bytes + t * kTileBytes + (uint32_t)row0 * 128u;
-            const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
-            // table entries are -1 for a missing neighbour and for rows past n_out
+              mbar_wait_warp_a(i_full_k, ir.phase);
+              PROF_ADD(pg_wi, pg_t0);
+              PROF_T0(pg_t0);
+              const int4 i0 = lds_v4(idx_k + t * (kTileM * 4u)), i1 = lds_v4(idx_k + t * (kTileM * 4u) + 16u);
+              const uint32_t szok = (kFull || (ch * 64 + c16 * 8) < (uint32_t)p.c_in) ? 16u : 0u;
+              const uint8_t *xb = x_lane + (size_t)ch * 128;
+              const uint32_t sb = dst_s + t * kTileBytes;
+              const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+              // table entries are -1 for a missing neighbour and for rows past n_out
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-              cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
-                         xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
-            cp_async_arrive_noinc(&a_full[ar.stage]);
-            PROF_ADD(pg_iss, pg_t0);
-            PROF_INC(pg_n);
+              for (int i = 0; i < 8; ++i)
+                cp_async16(sb ^ (uint32_t)(i * 144), xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes,
+                           ri[i] >= 0 ? szok : 0u);
+              cp_async_arrive_noinc_a(a_full_s);
+              // Release the index slot only now: the copies above consumed every loaded
+              // index, so the loads have completed.  (An asm LDS followed directly by the
+              // asm arrive carries no dependence; the arrive then overtook the load and the
+              // index warp overwrote the slot under it - a few wrong rows, run to run.)
+              __syncwarp();
+              if (lane == 0) mbar_arrive_a(i_empty_k);
+              PROF_ADD(pg_iss, pg_t0);
+              PROF_INC(pg_n);
+            }
+            ar.advance(S);
           }
-          ar.advance(S);
+          seen |= bits;
+          ir.advance(kIdxSlots);
         }
-        seen |= bits;
-        ir.advance(kIdxSlots);
       }
       ++it;
     }

@@ -75,11 +75,16 @@ __device__ __forceinline__ bool mbar_try_wait_short(uint64_t *bar, uint32_t pari
 // to a word of mapped host memory (it survives the dead context); everything is
 // inline - a call in this path would force spills into the hot loops.
 static __device__ unsigned int *mk_hang_slot = nullptr;   // set once per translation unit by the launcher
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int budget = 1) {
+// `sleep_ns` > 0 backs off between polls: the hinted try_wait (NANOSLEEP.SYNCS) comes
+// back on every barrier event of the CTA, so a warp that waits long by construction
+// (the epilogue: a whole group) re-polls thousands of times - 20 % of all
+// instructions of the forward kernel (ncu source view) in a kernel bound by issue.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int budget = 1, uint32_t sleep_ns = 0) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
   long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
+    if (sleep_ns) __nanosleep(sleep_ns);
     if ((++spins & 0xFFFFu) == 0) {                   // clock read off the common path
       const long long now = clock64();
       if (t0 == 0) {
@@ -127,10 +132,54 @@ __device__ __forceinline__ void mbar_wait_shared(uint64_t *bar, uint32_t parity,
 // with all 32 lanes of two dozen warps saturates the barrier unit and slows the
 // arrivals everybody is waiting for (measured: 0.82 ms of pure spin overhead
 // per 0.2 M stages).
-__device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, uint32_t parity, int budget = 1) {
-  mbar_wait(bar, parity, budget);
+__device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, uint32_t parity, int budget = 1,
+                                               uint32_t sleep_ns = 0) {
+  mbar_wait(bar, parity, budget, sleep_ns);
   __syncwarp();
 }
+// ---- shared-space forms (32-bit shared address) -----------------------------------
+// The hot producer loops keep shared addresses as 32-bit integers: through a
+// generic pointer the compiler emits generic LD/ST and a cvta per barrier
+// operation, and those loops are bound by instruction issue.
+__device__ __forceinline__ uint32_t lds_u8(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+  return v;
+}
+__device__ __forceinline__ int4 lds_v4(uint32_t saddr) {
+  int4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(saddr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t saddr, uint32_t v) {
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive_noinc_a(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity), "r"(0x989680u)
+      : "memory");
+  return ok != 0;
+}
+// mbar_wait_warp on a shared address; the (rare) slow path is the pointer form with its watchdog
+__device__ __forceinline__ void mbar_wait_warp_a(uint32_t bar, uint32_t parity) {
+  if (!mbar_try_wait_a(bar, parity)) mbar_wait((uint64_t *)__cvta_shared_to_generic(bar), parity);
+  __syncwarp();
+}
+
 // ---- async copies -----------------------------------------------------------
 // 16-byte LDGSTS; src_bytes == 0 writes 16 zero bytes without touching memory
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src, uint32_t src_bytes) {
