@@ -349,6 +349,8 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     const uint32_t dst_lane = smem_u32(a_ring) + (uint32_t)row0 * 128u + ((uint32_t)c16 << 4);
     const uint32_t idx_lane = smem_u32(idx_ring) + (uint32_t)row0 * 4u;
     const uint8_t *x_lane = (const uint8_t *)p.x + (size_t)c16 * 16;
+    asm volatile("" : "+l"(x_lane));   // keep the lane's base in a register pair: one IMAD.WIDE per row instead of
+                                       // IMAD.WIDE + a 64-bit add of the parameter re-read from the constant bank
     const uint32_t b_a_full = smem_u32(a_full), b_a_empty = smem_u32(a_empty);
     const uint32_t b_i_full = smem_u32(i_full), b_i_empty = smem_u32(i_empty);
     const uint32_t tickets_s = smem_u32(tickets);
@@ -413,6 +415,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               const int4 i0 = lds_v4(idx_k + t * (kTileM * 4u)), i1 = lds_v4(idx_k + t * (kTileM * 4u) + 16u);
               const uint32_t szok = (kFull || (ch * 64 + c16 * 8) < (uint32_t)p.c_in) ? 16u : 0u;
               const uint8_t *xb = x_lane + (size_t)ch * 128;
+              asm volatile("" : "+l"(xb));   // one register pair: row address = a single IMAD.WIDE
               const uint32_t sb = dst_s + t * kTileBytes;
               const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
               // table entries are -1 for a missing neighbour and for rows past n_out

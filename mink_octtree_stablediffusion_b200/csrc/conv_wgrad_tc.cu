@@ -189,12 +189,20 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     // waits with in-order release).  Warp q of a team moves panel rows
     // [32q, 32q+32); lane = (rsub, c16): instruction i moves 16-byte chunk c16 of
     // rows 32q + 8*rsub + i (four 128-byte feature rows per warp instruction)
-    const uint32_t a_base = smem_u32(a_ring);
     const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
     const uint32_t team = (uint32_t)warp >> 2;
     const int q = warp & 3;
     const int c16 = lane & 7, rsub = lane >> 3;
     const int row0 = 32 * q + 8 * rsub;
+    // The loop is bound by instruction issue: lane-constant address parts are computed
+    // once and shared memory is addressed in its own space (see conv_tc.cu).  Destination
+    // of copy i: bits 4-6 = c16 ^ i (swizzle), bits 7-9 = i (row in the 8-row atom) = an
+    // XOR with i * 144, the atom base having those bits clear.
+    const uint32_t dst_lane = smem_u32(a_ring) + (uint32_t)row0 * 128u + ((uint32_t)c16 << 4);
+    const uint32_t idx_lane = smem_u32(idx_ring) + (uint32_t)row0 * 4u;
+    const uint8_t *x_lane = (const uint8_t *)p.x + (size_t)c16 * 16;
+    const uint32_t b_a_full = smem_u32(a_full), b_a_empty = smem_u32(a_empty);
+    const uint32_t b_i_full = smem_u32(i_full), b_i_empty = smem_u32(i_empty);
     Ring ir, ar;
     uint32_t nstage = 0;                           // stages so far
     WP_DECL(g_wi = 0, g_wa = 0, g_is = 0, g_t0 = 0, g_start = 0, g_blk = 0, g_b0 = 0, g_sch = 0, g_s0 = 0;)
@@ -224,36 +232,42 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
         int pi = 0;
         if (p.pa > 1) pi = __shfl_sync(0xffffffffu, hf ? uc.pi1 : uc.pi0, u);
         const uint32_t szok = (real && (pi * 64 + c16 * 8) < p.c_in) ? 16u : 0u;
-        const uint8_t *xb = (const uint8_t *)p.x + (size_t)pi * 128 + (size_t)c16 * 16;
+        const uint8_t *xb = x_lane + (size_t)pi * 128;
+        asm volatile("" : "+l"(xb));   // one register pair: row address = a single IMAD.WIDE
         Ring as = ar;
         as.skip(rank, S);
         int4 i0 = make_int4(-1, -1, -1, -1), i1 = i0;
+        uint32_t i_empty_s = 0;
         if (real) {
           // real panels before this one: both halves of the pairs below u, and the first half of u
           Ring is = ir;
           is.skip((uint32_t)__popc(ts.p0 & below) + (uint32_t)__popc(ts.p1 & below) + (hf ? ((ts.p0 >> u) & 1u) : 0u),
                   kIdxSlots);
           WP_T0(g_t0);
-          mbar_wait_warp(&i_full[is.stage], is.phase);
+          mbar_wait_warp_a(b_i_full + is.stage * 8u, is.phase);
           WP_ADD(g_wi, g_t0);
-          const int4 *ip = reinterpret_cast<const int4 *>(idx_ring + is.stage * kTileM + row0);
-          i0 = ip[0];
-          i1 = ip[1];
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&i_empty[is.stage]);
+          i0 = lds_v4(idx_lane + is.stage * (kTileM * 4u));
+          i1 = lds_v4(idx_lane + is.stage * (kTileM * 4u) + 16u);
+          i_empty_s = b_i_empty + is.stage * 8u;
         }
         WP_T0(g_t0);
-        mbar_wait_warp(&a_empty[as.stage], as.phase ^ 1u);
+        mbar_wait_warp_a(b_a_empty + as.stage * 8u, as.phase ^ 1u);
         WP_ADD(g_wa, g_t0);
         WP_T0(g_t0);
-        const uint32_t sb = a_base + as.stage * kStageBytes + hf * kPanelBytes + (uint32_t)row0 * 128u;
+        const uint32_t sb = dst_lane + as.stage * kStageBytes + hf * kPanelBytes;
         const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
         if (!(p.knock & 1))
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          cp_async16(sb + (uint32_t)i * 128u + (uint32_t)((c16 ^ i) << 4),
-                     xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
-        cp_async_arrive_noinc(&a_full[as.stage]);
+          cp_async16(sb ^ (uint32_t)(i * 144), xb + (size_t)(uint32_t)max(ri[i], 0) * row_bytes, ri[i] >= 0 ? szok : 0u);
+        cp_async_arrive_noinc_a(b_a_full + as.stage * 8u);
+        if (real) {
+          // release the index slot only after the copies consumed every loaded index (an
+          // asm LDS followed directly by the asm arrive carries no dependence: the arrive
+          // can overtake the load and the slot is overwritten under it)
+          __syncwarp();
+          if (lane == 0) mbar_arrive_a(i_empty_s);
+        }
         WP_ADD(g_is, g_t0);
         WP_ADD(g_blk, g_b0);
       }
