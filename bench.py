@@ -380,10 +380,11 @@ def run_engine(args):
                        "l2": "working set (features, grads, neighbour table ~0.7 GB) exceeds the 126 MB L2"},
             "roofline": {"bound": "tensor", "kernel": "conv forward (%s)" % ("tcgen05" if conv_path else "simt"),
                          "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
-                         # dram__bytes_read+write of one k_conv_tc launch at R=271, ncu --set full
-                         # (profiles/r1_ncu_full_conv.csv); algorithmic bytes are x + y + neighbour table
-                         "traffic": 330.7e6 if (conv_path and R == R_FULL) else None,
-                         "alg_bytes_per_launch": int(n * (C_IN + C_OUT) * 2 + 4 * KS ** 3 * n),
+                         # dram__bytes_read+write of one k_conv_tc launch at R=271 on the tile-ordered table,
+                         # ncu --set full (profiles/r1d_ncu_full_conv_tile_ordered.csv); algorithmic bytes
+                         # are x + y + neighbour table + output-row permutation
+                         "traffic": 303.7e6 if (conv_path and R == R_FULL) else None,
+                         "alg_bytes_per_launch": int(n * (C_IN + C_OUT) * 2 + 4 * KS ** 3 * n + 4 * n),
                          "peak_source": pk["source"] + " (sustained bf16: kernel timed inside the step loop)",
                          "useful_flops_per_launch": flops_pass},
             "stages": {"conv_fwd_ms": fwd_ms, "conv_bwd_ms": bwd_ms,

@@ -9,8 +9,8 @@
 // SAME neighbour pattern grouped into the same tiles touch ~16 offsets at 70 %.
 //
 // mk_kmap_tile_order computes, from the finished table, a permutation `order` of
-// the table's columns (slot -> row) sorted by (batch, 2^b-voxel block, neighbour
-// pattern) and the table re-laid in slot order.  Blocks keep the gathers of
+// the table's columns (slot -> row) sorted by (hash of batch and 2^b-voxel block,
+// neighbour pattern) and the table re-laid in slot order.  Blocks keep the gathers of
 // concurrently processed tiles inside a few MB of the feature matrix (L2).  The
 // engine-visible row order of the coordinate map is NOT changed: the convolution
 // writes output row order[slot] (mk_conv_fwd_rows) and the weight gradient reads
@@ -24,10 +24,11 @@
 
 namespace mk {
 
-// key = [batch:8 | x>>b : 8 | y>>b : 8 | z>>b : 8 | pattern : 32]; coordinates are
-// 16-bit signed in the engine (hash key packing), so with b >= 8 the block
-// fields are exact; with smaller b distant blocks may share a key, which costs
-// locality only.  pattern = bit k set iff nbr[k, row] >= 0 (first 32 offsets).
+// key = [hash16(batch, x>>b, y>>b, z>>b) | pattern : 32], 48 significant bits = six
+// 8-bit passes of the radix sort instead of eight.  Rows of one block always share
+// the hash; distinct blocks that collide merely share tiles where their patterns
+// agree, which costs a little locality and nothing else.  pattern = bit k set iff
+// nbr[k, row] >= 0 (first 32 offsets).
 __global__ void k_order_key(const int32_t *__restrict__ nbr, int64_t n, int64_t ld, int K,
                             const int32_t *__restrict__ coords, int ncols, int bl,
                             unsigned long long *__restrict__ keys, int32_t *__restrict__ rows) {
@@ -39,8 +40,9 @@ __global__ void k_order_key(const int32_t *__restrict__ nbr, int64_t n, int64_t 
   uint32_t blk = 0;
   if (coords) {
     const int32_t *c = coords + r * ncols;
-    blk = ((uint32_t)__ldg(c) & 0xFFu) << 24;
-    for (int d = 1; d < ncols && d < 4; ++d) blk |= ((uint32_t)(__ldg(c + d) >> bl) & 0xFFu) << (8 * (3 - d));
+    blk = (uint32_t)__ldg(c) * 0x9E3779B1u;
+    for (int d = 1; d < ncols; ++d) blk = (blk ^ (uint32_t)(__ldg(c + d) >> bl)) * 0x85EBCA6Bu;
+    blk = (blk ^ (blk >> 15)) & 0xFFFFu;
   }
   keys[r] = ((unsigned long long)blk << 32) | pat;
   rows[r] = (int32_t)r;
@@ -55,6 +57,8 @@ __global__ void k_permute_table(const int32_t *__restrict__ src, const int32_t *
   for (int k = 0; k < K; ++k)
     dst[(int64_t)k * ld + slot] = r >= 0 ? __ldg(src + (int64_t)k * ld + r) : -1;
 }
+
+constexpr int kKeyBits = 48;
 
 static inline size_t align256o(size_t b) { return (b + 255) & ~(size_t)255; }
 
@@ -96,7 +100,7 @@ extern "C" int mk_kmap_tile_order(const int32_t *nbr, int64_t n_rows, int64_t ld
     k_order_key<<<(unsigned)((n_rows + 255) / 256), 256, 0, st>>>(nbr, n_rows, ld, K, coords, ncols, block_log2,
                                                                    keys_in, rows_in);
     MK_LAUNCH_CHECK();
-    MK_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, rows_in, order, (int)n_rows, 0, 64,
+    MK_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, rows_in, order, (int)n_rows, 0, kKeyBits,
                                             st));
   }
   k_permute_table<<<(unsigned)((ld + 255) / 256), 256, 0, st>>>(nbr, order, n_rows, ld, K, nbr_ordered);
