@@ -43,8 +43,9 @@ constexpr int kTileBytes = kTileM * 128;   // one gathered tile: 128 rows x 64 1
 // one A stage = the T tiles of a group under one (offset, channel chunk): T * kTileBytes
 constexpr int kGatherTeams = 4;              // stages in flight on the producer side
 constexpr int kGatherWarps = 4 * kGatherTeams;   // 4 warps (32 rows each) per stage
-constexpr int kMmaWarps = 1;   // stages must be released in order: the parity waits of the producer
-                               // teams are only alias-free when consumption is in order
+constexpr int kMmaWarps = 2;   // tile t of a stage belongs to MMA warp t % kMmaWarps.  Every MMA warp waits on
+                               // every stage and commits to its release barrier (count kMmaWarps), so stages are
+                               // still released in order: the producers' parity waits stay alias-free
 constexpr int kWarpIdx = 4, kWarpWeights = 5, kWarpMma0 = 6, kWarpGather0 = kWarpMma0 + kMmaWarps;
 constexpr int kNumThreadsTC = 32 * (kWarpGather0 + kGatherWarps);
 constexpr int kSchedCopies = 2 + kGatherWarps;
@@ -215,10 +216,10 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   const int acc_stride = (p.NT + 31) & ~31;
 
   if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u); mbar_init(&a_empty[s], 1); }
-    for (uint32_t s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u); mbar_init(&a_empty[s], kMmaWarps); }
+    for (uint32_t s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], kMmaWarps); mbar_init(&t_empty[s], 4); }
     fence_barrier_init();
   }
   if (warp == kWarpMma0) tmem_alloc_512(tmem_slot);
@@ -451,8 +452,8 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
       }
       mbar_arrive(&a_full[ar.stage]);
     }
-  } else if (warp == kWarpMma0) {
-    // ===================== MMA issuer: driven by tickets =====================
+  } else if (warp >= kWarpMma0 && warp < kWarpMma0 + kMmaWarps) {
+    // ===================== MMA issuers: driven by tickets =====================
     // The whole warp runs the loop converged on warp-uniform values (the ticket is
     // broadcast with a shuffle), so that the descriptors live in uniform registers
     // and one elected lane issues back-to-back UTCHMMA without per-operand R2UR.
@@ -462,20 +463,21 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
       // descriptor template: SBO = 1024 B (8-row atoms), LBO = 16 B (unused for one
       // 128-byte K atom), version 1, SWIZZLE_128B; the start address is added per MMA
       const uint64_t desc0 = smem_desc_sw128(0, 16, 1024);
+      const uint32_t mw = (uint32_t)(warp - kWarpMma0);
       uint32_t s = 0, ph = 0, bs = 0, bph = 0;
       PROF_DECL(pm_wa = 0, pm_wt = 0, pm_wb = 0, pm_iss = 0, pm_n = 0, pm_t0 = 0, pm_start = PROF_NOW(), pm_f = 0, pm_m = 0, pm_c = 0;)
       for (;;) {
         PROF_T0(pm_t0);
-        mbar_wait(&a_full[s], ph);
+        mbar_wait_shared(&a_full[s], ph);
         PROF_ADD(pm_wa, pm_t0);
         const uint32_t tk = __shfl_sync(0xffffffffu, *(volatile uint32_t *)&tickets[s], 0);
         if (tk & kTkEnd) break;
         const uint32_t h = (tk >> 8) & 1u;
         PROF_T0(pm_t0);
-        if (tk & kTkGroupBegin) mbar_wait(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
+        if (tk & kTkGroupBegin) mbar_wait_shared(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
         PROF_ADD(pm_wt, pm_t0);
         PROF_T0(pm_t0);
-        mbar_wait(&b_full[bs], bph);
+        mbar_wait_shared(&b_full[bs], bph);
         PROF_ADD(pm_wb, pm_t0);
         PROF_T0(pm_t0);
         tc_fence_after();
@@ -489,7 +491,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
           PROF_T0(pq_t0);
 #pragma unroll
           for (int t = 0; t < kMaxT; ++t) {
-            if (!((tk >> t) & 1u)) continue;
+            if ((uint32_t)(t % kMmaWarps) != mw || !((tk >> t) & 1u)) continue;
             const uint32_t d = d0 + (uint32_t)(t * acc_stride);
             const uint64_t ad0 = desc0 | (uint64_t)(((a0 + (uint32_t)t * kTileBytes) & 0x3FFFFu) >> 4);
             const uint32_t acc0 = (tk >> (4 + t)) & 1u;
