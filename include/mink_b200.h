@@ -172,8 +172,7 @@ int mk_kmap_tile_mask(const int32_t *nbr, int64_t n_rows, int64_t ld, int K,
  * same table with column s = old column order[s] (padding -1).  Row indices
  * INSIDE the table are untouched.  coords may be NULL (pattern only).  The
  * coordinate map's row order does not change: mk_conv_fwd_rows writes row
- * order[s]; for the weight gradient the caller gathers dy through `order`
- * (mk_rows_gather) and calls mk_conv_wgrad on the ordered table. */
+ * order[s]; the weight gradient reads dy row order[s] (mk_conv_wgrad_rows). */
 int64_t mk_kmap_tile_order_workspace_bytes(int64_t n_rows);
 int mk_kmap_tile_order(const int32_t *nbr, int64_t n_rows, int64_t ld, int K,
                        const int32_t *coords, int ncols, int block_log2,
@@ -223,6 +222,16 @@ int mk_conv_wgrad(int dtype, const void *x, const void *dy,
                   int64_t n_out, int64_t n_in, int K,
                   int c_in, int c_out, void *dw, void *workspace,
                   void *stream);
+/* mk_conv_wgrad on a tile-ordered table: table column o pairs with dy row
+ * dy_rows[o] (the `order` of mk_kmap_tile_order; 16-byte aligned), read inside
+ * the kernel with TMA tile::gather4 - no permuted copy of dy is made.  Served
+ * by the tensor-core path only (MK_EUNSUPPORTED otherwise); dy_rows == NULL is
+ * mk_conv_wgrad. */
+int mk_conv_wgrad_rows(int dtype, const void *x, const void *dy,
+                       const int32_t *dy_rows, const int32_t *nbr,
+                       const uint32_t *tile_mask, int64_t ld, int64_t n_out,
+                       int64_t n_in, int K, int c_in, int c_out, void *dw,
+                       void *workspace, void *stream);
 /* which implementation the last mk_conv_* call on this thread used:
  * 0 = SIMT tiled kernel, 1 = tcgen05/TMEM kernel */
 int mk_conv_last_path(void);

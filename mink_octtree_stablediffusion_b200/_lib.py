@@ -52,6 +52,7 @@ PROTOTYPES = {
     "mk_kmap_tile_order_workspace_bytes": (_i64, [_i64]),
     "mk_kmap_tile_order": (_i, [_p, _i64, _i64, _i, _p, _i, _i, _p, _p, _p, _p]),
     "mk_conv_wgrad": (_i, [_i, _p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _p, _p]),
+    "mk_conv_wgrad_rows": (_i, [_i, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _p, _p]),
     "mk_conv_last_path": (_i, []),
     "mk_conv_force_simt": (_i, [_i]),
     "mk_pool_fwd": (_i, [_i, _i, _p, _p, _i64, _i64, _i, _i, _p, _p, _p, _p]),

@@ -241,18 +241,20 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
     dw = torch.empty((km.K, c_in, c_out), dtype=x.dtype, device=x.device)
     code = _dtype_code(x)
     ws = _workspace(lib, code, km.n_out, km.K, c_in, c_out, x.device)
-    table, mask = km.nbr, None
+    table, mask, order = km.nbr, None, None
     if km.n_out > 0 and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
-        # the ordered table pairs column s with dy row order[s]
+        # the ordered table pairs column s with dy row order[s]; the kernel reads dy through it
         order, table, mask = _ordered(mgr, km)
-        dy_o = torch.empty_like(dy)
-        _lib.check(lib.mk_rows_gather(_ptr(dy), _ptr(order), km.n_out, dy.size(1) * dy.element_size(), _ptr(dy_o),
-                                      _stream()))
-        dy = dy_o
+        if (x.data_ptr() | dy.data_ptr()) & 15:
+            # views at odd offsets fall to the SIMT kernel, which wants dy in table order
+            dy_o = torch.empty_like(dy)
+            _lib.check(lib.mk_rows_gather(_ptr(dy), _ptr(order), km.n_out, dy.size(1) * dy.element_size(), _ptr(dy_o),
+                                          _stream()))
+            dy, order = dy_o, None
     if mask is None:
         mask = _fwd_mask(mgr, km)
-    _lib.check(lib.mk_conv_wgrad(code, _ptr(x), _ptr(dy), _ptr(table), _ptr(mask), km.ld, km.n_out, x.size(0), km.K,
-                                 c_in, c_out, _ptr(dw), _ptr(ws), _stream()))
+    _lib.check(lib.mk_conv_wgrad_rows(code, _ptr(x), _ptr(dy), _ptr(order), _ptr(table), _ptr(mask), km.ld, km.n_out,
+                                      x.size(0), km.K, c_in, c_out, _ptr(dw), _ptr(ws), _stream()))
     return dw
 
 

@@ -24,9 +24,10 @@ int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w,
 bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
 int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_wgrad_tc(int dtype, const void *x, const void *dy,
-                  const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
-                  int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
-                  void *dw, void *workspace, cudaStream_t st);
+                  const int32_t *dy_rows, const int32_t *nbr,
+                  const uint32_t *tile_mask, int64_t ld, int64_t n_out,
+                  int64_t n_in, int K, int c_in, int c_out, void *dw,
+                  void *workspace, cudaStream_t st);
 
 static thread_local int g_last_path = 0;
 static int g_force_simt = 0;
@@ -114,11 +115,11 @@ int mk_conv_fwd_rows(int dtype, const void *x, const void *w, int transpose_w,
                                 n_out, K, c_in, c_out, y, st);
 }
 
-int mk_conv_wgrad(int dtype, const void *x, const void *dy,
-                  const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
-                  int64_t n_out, int64_t n_in, int K,
-                  int c_in, int c_out, void *dw, void *workspace,
-                  void *stream) {
+int mk_conv_wgrad_rows(int dtype, const void *x, const void *dy,
+                       const int32_t *dy_rows, const int32_t *nbr,
+                       const uint32_t *tile_mask, int64_t ld, int64_t n_out,
+                       int64_t n_in, int K, int c_in, int c_out, void *dw,
+                       void *workspace, void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
   if (rc) return rc;
   MK_CHECK_ARG(n_in >= 0, "n_in must be >= 0");
@@ -129,14 +130,29 @@ int mk_conv_wgrad(int dtype, const void *x, const void *dy,
   cudaStream_t st = (cudaStream_t)stream;
   if (!g_force_simt && workspace && n_in > 0 && n_out > 0 &&
       tc_layout_ok(x, dy, nbr, ld) &&
+      (dy_rows == nullptr || ((uintptr_t)dy_rows & 15) == 0) &&
       conv_wgrad_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
-    return conv_wgrad_tc(dtype, x, dy, nbr, tile_mask, ld, n_out, n_in, K,
-                         c_in, c_out, dw, workspace, st);
+    return conv_wgrad_tc(dtype, x, dy, dy_rows, nbr, tile_mask, ld, n_out,
+                         n_in, K, c_in, c_out, dw, workspace, st);
+  }
+  if (dy_rows) {
+    set_error("mk_conv_wgrad_rows: dy_rows is served by the tensor-core path "
+              "only (16-bit dtype, eligible shape, 16-byte aligned pointers)");
+    return MK_EUNSUPPORTED;
   }
   g_last_path = 0;
   return conv_wgrad_simt_dispatch(dtype, x, dy, nbr, ld, n_out, K, c_in,
                                   c_out, dw, workspace, st);
+}
+
+int mk_conv_wgrad(int dtype, const void *x, const void *dy,
+                  const int32_t *nbr, const uint32_t *tile_mask, int64_t ld,
+                  int64_t n_out, int64_t n_in, int K,
+                  int c_in, int c_out, void *dw, void *workspace,
+                  void *stream) {
+  return mk_conv_wgrad_rows(dtype, x, dy, nullptr, nbr, tile_mask, ld, n_out,
+                            n_in, K, c_in, c_out, dw, workspace, stream);
 }
 
 }  // extern "C"

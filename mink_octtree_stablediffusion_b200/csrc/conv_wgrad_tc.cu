@@ -71,6 +71,7 @@ struct Params {
   const void *x;          // [n_in, c_in]
   const int32_t *nbr;     // [K, ld]
   const uint32_t *mask;   // [ntiles, W]
+  const int32_t *dy_rows; // optional [n_out]: table column o pairs with dy row dy_rows[o] (tile-ordered table)
   float *partial;         // [X][K][c_in][c_out]
   int64_t ld, n_out, n_in;
   int K, W, c_in, c_out;
@@ -139,7 +140,8 @@ __device__ __forceinline__ TileSched tile_sched(const Params &p, const uint32_t 
 }  // namespace wg
 
 __global__ void __launch_bounds__(wg::kThreads, 1)
-k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CUtensorMap tmap_dy) {
+k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CUtensorMap tmap_dy,
+                const __grid_constant__ CUtensorMap tmap_dy_row) {
   using namespace wg;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -175,7 +177,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     *inited_slot = 0u;
     fence_barrier_init();
   }
-  if (warp == kWarpDy && lane == 0) tma_prefetch_desc(&tmap_dy);
+  if (warp == kWarpDy && lane == 0) tma_prefetch_desc(p.dy_rows ? &tmap_dy_row : &tmap_dy);
   if (warp == kWarpMma) tmem_alloc_512(tmem_slot);
   tc_fence_before();
   __syncthreads();
@@ -440,7 +442,27 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
       for (int m = 0; m < kMmaWarps; ++m) mbar_wait_warp(&b_empty[br.stage * kMmaWarps + m], br.phase ^ 1u);
-      if (lane == 0) {
+      if (p.dy_rows) {
+        // rows through the permutation: lane l brings rows 4l..4l+3 of the tile with one
+        // tile::gather4 per 64-channel panel (same swizzled image as the tiled load);
+        // columns past n_out get an out-of-range row index = zero fill
+        const int64_t o = (int64_t)tile * kTileM + 4 * lane;
+        int4 r;
+        if (o + 3 < p.n_out) {
+          r = __ldg(reinterpret_cast<const int4 *>(p.dy_rows + o));
+        } else {
+          const int32_t oob = (int32_t)p.n_out;
+          r.x = o + 0 < p.n_out ? __ldg(p.dy_rows + o + 0) : oob;
+          r.y = o + 1 < p.n_out ? __ldg(p.dy_rows + o + 1) : oob;
+          r.z = o + 2 < p.n_out ? __ldg(p.dy_rows + o + 2) : oob;
+          r.w = oob;
+        }
+        if (lane == 0) mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
+        __syncwarp();
+        for (int pn = 0; pn < p.pb; ++pn)
+          tma_gather4(b_base + br.stage * b_bytes + (uint32_t)pn * kPanelBytes + (uint32_t)lane * 512u, &tmap_dy_row,
+                      ns * p.NB + pn * 64, r, &b_full[br.stage]);
+      } else if (lane == 0) {
         mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
         for (int pn = 0; pn < p.pb; ++pn)
           tma_load_2d(b_base + br.stage * b_bytes + (uint32_t)pn * kPanelBytes, &tmap_dy, ns * p.NB + pn * 64,
@@ -552,9 +574,9 @@ int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
   return (int64_t)(pl.partial_bytes + pl.mask_bytes + 256);
 }
 
-int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, const uint32_t *tile_mask,
-                  int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out, void *dw, void *workspace,
-                  cudaStream_t st) {
+int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_rows, const int32_t *nbr,
+                  const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                  void *dw, void *workspace, cudaStream_t st) {
   using namespace wg;
   WPlan pl;
   if (!make_wplan(dtype, n_out, K, c_in, c_out, pl)) {
@@ -569,13 +591,15 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, 
     if (rc) return rc;
     tile_mask = mask;
   }
-  CUtensorMap tmap_dy;
+  CUtensorMap tmap_dy, tmap_dy_row;
   {
     int rc = make_tmap_rows16(&tmap_dy, dtype, dy, n_out, c_out, 64, kTileM);
     if (rc) return rc;
+    rc = make_tmap_rows16(&tmap_dy_row, dtype, dy, n_out, c_out, 64, 1);   // tile::gather4 form
+    if (rc) return rc;
   }
   Params p;
-  p.x = x; p.nbr = nbr; p.mask = tile_mask; p.partial = partial;
+  p.x = x; p.nbr = nbr; p.mask = tile_mask; p.dy_rows = dy_rows; p.partial = partial;
   p.ld = ld; p.n_out = n_out; p.n_in = n_in;
   p.K = K; p.W = pl.W; p.c_in = c_in; p.c_out = c_out;
   p.pa = pl.pa; p.npairs = pl.npairs; p.ppg = pl.ppg; p.G = pl.G;
@@ -591,7 +615,7 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *nbr, 
     attr_set = true;
   }
   dim3 grid(pl.X, pl.G * pl.nsplit);
-  k_conv_wgrad_tc<<<grid, kThreads, pl.smem, st>>>(p, tmap_dy);
+  k_conv_wgrad_tc<<<grid, kThreads, pl.smem, st>>>(p, tmap_dy, tmap_dy_row);
   MK_LAUNCH_CHECK();
   const int64_t n_w = (int64_t)K * c_in * c_out;
   const unsigned blocks = (unsigned)ceil_div(n_w / 4, 256);

@@ -131,14 +131,18 @@ def rows_gather(src, idx):
     return dst
 
 
-def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None):
+def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None, dy_rows=None):
     lib = _lib.load()
     c_in, c_out = x.shape[1], dy.shape[1]
     dw = torch.empty((K, c_in, c_out), dtype=x.dtype, device="cuda")
     ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
                      device="cuda")
-    _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), P(mask), ld, n_out, x.shape[0], K, c_in, c_out, P(dw),
-                                 P(ws), S()))
+    if dy_rows is None:
+        _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), P(mask), ld, n_out, x.shape[0], K, c_in, c_out,
+                                     P(dw), P(ws), S()))
+    else:
+        _lib.check(lib.mk_conv_wgrad_rows(DT[x.dtype], P(x), P(dy), P(dy_rows), P(nbr), P(mask), ld, n_out, x.shape[0],
+                                          K, c_in, c_out, P(dw), P(ws), S()))
     return dw
 
 

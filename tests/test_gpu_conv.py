@@ -235,6 +235,12 @@ def test_tile_ordered_table(R, order, with_coords):
     w0 = abi.conv_wgrad(x, dy, nbr, ld, n, 27)
     w1 = abi.conv_wgrad(x, abi.rows_gather(dy, perm), nbr_t, ld, n, 27)
     assert float((w0.float() - w1.float()).abs().max() / w0.float().abs().max()) <= 1e-2
-    # fp32 has no tensor-core path: an output permutation must be refused, not ignored
+    # dy read through the permutation inside the kernel (TMA gather4) = the pre-gathered copy, bit for bit
+    w2 = abi.conv_wgrad(x, dy, nbr_t, ld, n, 27, dy_rows=perm)
+    assert abi.last_path() == 1
+    assert torch.equal(w1, w2)
+    # fp32 has no tensor-core path: a row permutation must be refused, not ignored
     with pytest.raises(RuntimeError):
         abi.conv_fwd_rows(x.float(), w.float(), nbr_t, ld, n, perm)
+    with pytest.raises(RuntimeError):
+        abi.conv_wgrad(x.float(), dy.float(), nbr_t, ld, n, 27, dy_rows=perm)
