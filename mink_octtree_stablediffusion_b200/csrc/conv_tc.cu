@@ -406,6 +406,13 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               }
               if (!((bits >> t) & 1u)) {
                 mbar_arrive_a(a_full_s);             // nothing to gather: stand in for the cp.async arrivals
+                // The indices are not needed, but the team must still OBSERVE this phase of the
+                // slot's barrier: a parity wait is only sound for a waiter that has seen every
+                // earlier phase.  A team that skipped here could run a whole idx ring ahead (the A
+                // ring is deeper than the idx ring when T < 4) and find the slot's next wait
+                // satisfied by THIS phase still in flight - it then gathered through stale
+                // indices (seen as an illegal address with the T = 2 plan).
+                mbar_wait_warp_a(i_full_k, ir.phase);
                 if (lane == 0) mbar_arrive_a(i_empty_k);
                 continue;
               }
@@ -419,6 +426,22 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
               asm volatile("" : "+l"(xb));   // one register pair: row address = a single IMAD.WIDE
               const uint32_t sb = dst_s + t * kTileBytes;
               const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+#ifdef MK_TC_CHECK
+              // development check: a gathered index outside the feature matrix (a pipeline bug:
+              // the slot was read before it was loaded or after it was overwritten)
+              for (int i = 0; i < 8; ++i)
+                if (ri[i] >= (int32_t)p.n_in || ri[i] < -1) {
+                  unsigned int *hh = mk_hang_slot;
+                  if (hh) {
+                    hh[1] = blockIdx.x | (blockIdx.y << 16);
+                    hh[2] = (uint32_t)warp | (k << 8) | (t << 16) | (ir.stage << 20) | (ir.phase << 24) | (ar.stage << 25);
+                    hh[3] = (uint32_t)ri[i];
+                    hh[0] = 0xBAD1D000u | (uint32_t)i;
+                    __threadfence_system();
+                  }
+                  asm volatile("trap;");
+                }
+#endif
               // table entries are -1 for a missing neighbour and for rows past n_out
 #pragma unroll
               for (int i = 0; i < 8; ++i)
@@ -600,7 +623,8 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   // development knobs (tuning sweeps): MK_TC_T / MK_TC_BSTAGES / MK_TC_ISLOTS
   if (const char *e = getenv("MK_TC_T")) pl.T = std::max(1, std::min(pl.T, atoi(e)));
   if (const char *e = getenv("MK_TC_BSTAGES")) pl.b_stages = std::max(2, std::min(kMaxBStages, atoi(e)));
-  if (const char *e = getenv("MK_TC_ISLOTS")) pl.i_slots = std::max(2, std::min(kMaxIdxSlots, atoi(e)));
+  // (a multiple of 4: the teams that use an idx slot must be the same every time round the ring)
+  if (const char *e = getenv("MK_TC_ISLOTS")) pl.i_slots = std::max(4, std::min(kMaxIdxSlots, atoi(e) & ~3));
   pl.W = (K + 31) / 32;
   const size_t b_bytes = (size_t)pl.NT * 128;
   const size_t fixed = 1024 /*align slack*/ + pl.b_stages * b_bytes + (size_t)pl.i_slots * pl.T * kTileM * 4 +

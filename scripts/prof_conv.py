@@ -116,8 +116,15 @@ def main():
         print(f"fwd   {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered)", flush=True)
         t, _ = timed(lambda: abi.conv_fwd_rows(dy, w, nbr_o, ld, n, perm, transpose_w=1, kflip=1, mask=mask_o), args.iters)
         print(f"dgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered)", flush=True)
-        t, _ = timed(lambda: abi.conv_wgrad(x, abi.rows_gather(dy, perm), nbr_o, ld, n, 27, mask=mask_o), args.iters)
-        print(f"wgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered, incl. dy gather)", flush=True)
+        t, _ = timed(lambda: abi.conv_wgrad(x, dy, nbr_o, ld, n, 27, mask=mask_o, dy_rows=perm), args.iters)
+        print(f"wgrad {t:.3f} ms  {fl / t / 1e9:.1f} TFLOP/s useful  (tile-ordered, dy read through the order)", flush=True)
+        for cfg in [c_ for c_ in args.sweep.split(";") if c_]:
+            T_, B_, I_ = cfg.split(",")
+            os.environ["MK_TC_T"], os.environ["MK_TC_BSTAGES"], os.environ["MK_TC_ISLOTS"] = T_, B_, I_
+            t, _ = timed(lambda: abi.conv_fwd_rows(x, w, nbr_o, ld, n, perm, mask=mask_o), args.iters)
+            t2, _ = timed(lambda: abi.conv_fwd_rows(dy, w, nbr_o, ld, n, perm, transpose_w=1, kflip=1, mask=mask_o),
+                          args.iters)
+            print(f"T={T_} B={B_} I={I_}: fwd {t:.3f} ms dgrad {t2:.3f} ms (tile-ordered)", flush=True)
         return
     for cfg in [c_ for c_ in args.sweep.split(";") if c_]:
         T_, B_, I_ = cfg.split(",")
@@ -142,4 +149,14 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    except Exception as e:
+        import ctypes
+        from mink_octtree_stablediffusion_b200 import _lib
+        print("FAILED:", str(e)[:100], flush=True)
+        w4 = (ctypes.c_uint * 4)()
+        rc = _lib.load().mk_debug_hang_words(w4)
+        print("watchdog rc", rc, "magic %x block (%d,%d) warp %d smem 0x%x parity %d" %
+              (w4[0], w4[1] & 0xFFFF, w4[1] >> 16, w4[2], w4[3] >> 1, w4[3] & 1), flush=True)
+        sys.exit(1)

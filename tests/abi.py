@@ -100,6 +100,10 @@ def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None, mask=None
     return y
 
 
+def tc_eligible(dtype, n_rows, K, c_in, c_out):
+    return bool(_lib.load().mk_conv_tc_eligible(DT[dtype], n_rows, K, c_in, c_out))
+
+
 def tile_order(nbr, n_rows, ld, K, coords_dev=None, block_log2=7):
     """(order [n_rows], table in tile order [K, ld])"""
     lib = _lib.load()

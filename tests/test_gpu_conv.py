@@ -200,6 +200,78 @@ def test_tensor_core_path_at_scale(R, order):
     assert abs(a - b) <= 1e-5 * scale and abs(a - cc) <= 1e-5 * scale
 
 
+@pytest.mark.parametrize("cin,cout", [(64, 256), (256, 64), (320, 320), (64, 320), (640, 320), (320, 960), (16, 16)])
+def test_tensor_core_wide_channels(cin, cout):
+    """Channel tuples of the diffusion UNet (320/640/960) and the other plan shapes
+    of the tcgen05 kernels (several 64-channel chunks, output split over CTAs, one tile per
+    group) on 50 k voxels, with and without the tile-ordered table: agreement with the fp32
+    CUDA-core path within the bf16 tolerance and bit-identical results from run to run."""
+    c = _northstar_cloud(60, "shuffled")
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    assert abi.tc_eligible(torch.bfloat16, n, 27, cin, cout)
+    perm, nbr_t = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(n, cin, generator=g).bfloat16().cuda()
+    dy = torch.randn(n, cout, generator=g).bfloat16().cuda()
+    w = (torch.randn(27, cin, cout, generator=g) / (27 * cin) ** 0.5).bfloat16().cuda()
+
+    def run(ordered):
+        if ordered:
+            y = abi.conv_fwd_rows(x, w, nbr_t, ld, n, perm)
+            gi = abi.conv_fwd_rows(dy, w, nbr_t, ld, n, perm, transpose_w=1, kflip=1)
+            gw = abi.conv_wgrad(x, dy, nbr_t, ld, n, 27, dy_rows=perm)
+        else:
+            y = abi.conv_fwd(x, w, nbr, ld, n)
+            gi = abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1)
+            gw = abi.conv_wgrad(x, dy, nbr, ld, n, 27)
+        assert abi.last_path() == 1, "tensor-core path expected"
+        return y, gi, gw
+
+    abi.force_simt(1)
+    try:
+        xf, dyf, wf = x.float(), dy.float(), w.float()
+        ref = (abi.conv_fwd(xf, wf, nbr, ld, n), abi.conv_fwd(dyf, wf, nbr, ld, n, transpose_w=1, kflip=1),
+               abi.conv_wgrad(xf, dyf, nbr, ld, n, 27))
+    finally:
+        abi.force_simt(0)
+    for ordered in (False, True):
+        a, b = run(ordered), run(ordered)
+        for u, v, r in zip(a, b, ref):
+            assert torch.equal(u, v)
+            err = float((u.float() - r).abs().max() / r.abs().max())
+            assert err <= 1e-2, (ordered, err)
+
+
+def test_tensor_core_plans_agree_under_load(monkeypatch):
+    """Regression for a pipeline race of the forward/dgrad kernel: with fewer than four tiles
+    per group the A ring is deeper than the neighbour-index ring, and a gather team whose tile
+    had no neighbour under an offset skipped the wait on that index slot, ran ahead and read the
+    slot's next round before it was loaded (wrong rows / an illegal address, about one launch in
+    thirty).  Every plan (tiles per group forced through the development knob MK_TC_T) must give
+    the bit-identical result of the default plan, launch after launch."""
+    c = _northstar_cloud(200, "sorted")
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    perm, nbr_t = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])
+    mask = abi.tile_mask(nbr_t, n, ld, 27)
+    g = torch.Generator().manual_seed(13)
+    dy = torch.randn(n, 64, generator=g).bfloat16().cuda()
+    w = (torch.randn(27, 64, 64, generator=g) / 40).bfloat16().cuda()
+    run = lambda: abi.conv_fwd_rows(dy, w, nbr_t, ld, n, perm, transpose_w=1, kflip=1, mask=mask)
+    monkeypatch.delenv("MK_TC_T", raising=False)
+    ref = run()
+    assert abi.last_path() == 1
+    for T, reps in (("2", 60), ("1", 30), ("3", 20), ("4", 20)):
+        monkeypatch.setenv("MK_TC_T", T)
+        for _ in range(reps):
+            assert torch.equal(run(), ref), T
+
+
 @pytest.mark.parametrize("R,order,with_coords", [(60, "sorted", True), (60, "shuffled", True), (40, "sorted", False)])
 def test_tile_ordered_table(R, order, with_coords):
     """mk_kmap_tile_order: `order` is a permutation, the ordered table is the table with its
