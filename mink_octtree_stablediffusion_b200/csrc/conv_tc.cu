@@ -82,6 +82,7 @@ struct ConvTCParams {
   const int32_t *out_rows; // optional [n_out]: table column o is output row out_rows[o] (tile-ordered maps)
   int64_t ld, n_out, n_in;
   int K, W, kflip;
+  int b_merged;           // weight ring = A ring (same depth): image s travels with stage s on the stage's barriers
   int c_in, c_out, nchunk, NT, T;
   int a_stages, b_stages, i_slots;
   int ngroups;
@@ -201,8 +202,9 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   const uint32_t kBStages = (uint32_t)p.b_stages, kIdxSlots = (uint32_t)p.i_slots;
   const uint32_t idx_slot = (uint32_t)p.T * kTileM;   // entries per slot
   int32_t *idx_ring = (int32_t *)(b_ring + kBStages * b_bytes);
-  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * idx_slot);   // per-role copies x kMaxK
-  uint32_t *tickets = (uint32_t *)(sched_all + kSchedCopies * kMaxK);   // [S]
+  const uint32_t sched_stride = ((uint32_t)p.K + 31u) & ~31u;            // bytes per role copy of the schedule
+  uint8_t *sched_all = (uint8_t *)(idx_ring + kIdxSlots * idx_slot);   // per-role copies x sched_stride
+  uint32_t *tickets = (uint32_t *)(sched_all + kSchedCopies * sched_stride);   // [S]
   uint64_t *bars = (uint64_t *)(tickets + 16);
   uint64_t *a_full = bars, *a_empty = a_full + S;
   uint64_t *b_full = a_empty + S, *b_empty = b_full + kBStages;
@@ -216,7 +218,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   const int acc_stride = (p.NT + 31) & ~31;
 
   if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u); mbar_init(&a_empty[s], kMmaWarps); }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u + (p.b_merged ? 1u : 0u)); mbar_init(&a_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
     for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], kMmaWarps); mbar_init(&t_empty[s], 4); }
@@ -292,7 +294,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     // ===================== neighbour-index prefetch =====================
     // one slot of the idx ring per offset: the T*128 table entries of the group; the
     // channel chunks of an offset reuse the slot
-    uint8_t *sched = sched_all + 0 * kMaxK;
+    uint8_t *sched = sched_all + 0 * sched_stride;
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
     PROF_DECL(pi_wait = 0, pi_t0 = 0;)
@@ -338,7 +340,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     const int gw = warp - kWarpGather0;
     const uint32_t team = (uint32_t)gw >> 2;
     const int q = gw & 3;
-    uint8_t *sched = sched_all + (2 + gw) * kMaxK;
+    uint8_t *sched = sched_all + (2 + gw) * sched_stride;
     const uint32_t sched_s = smem_u32(sched);
     const uint32_t row_bytes = (uint32_t)p.c_in * 2u;
     const int c16 = lane & 7, rsub = lane >> 3;
@@ -500,11 +502,11 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         if (tk & kTkGroupBegin) mbar_wait_shared(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
         PROF_ADD(pm_wt, pm_t0);
         PROF_T0(pm_t0);
-        mbar_wait_shared(&b_full[bs], bph);
+        if (!p.b_merged) mbar_wait_shared(&b_full[bs], bph);
         PROF_ADD(pm_wb, pm_t0);
         PROF_T0(pm_t0);
         tc_fence_after();
-        const uint64_t bd0 = desc0 | (uint64_t)(((b_base + bs * b_bytes) & 0x3FFFFu) >> 4);
+        const uint64_t bd0 = desc0 | (uint64_t)(((b_base + (p.b_merged ? s : bs) * b_bytes) & 0x3FFFFu) >> 4);
         const uint32_t d0 = tm_base + h * 256u;
         const uint32_t a0 = a_base + s * stage_bytes;
         if (elect_one()) {
@@ -535,7 +537,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
           PROF_ADD(pm_m, pq_t0);
           PROF_T0(pq_t0);
           umma_commit(&a_empty[s]);
-          umma_commit(&b_empty[bs]);
+          if (!p.b_merged) umma_commit(&b_empty[bs]);
           if (tk & kTkGroupEnd) umma_commit(&t_full[h]);
           PROF_ADD(pm_c, pq_t0);
         }
@@ -545,11 +547,11 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         if (++bs == kBStages) { bs = 0; bph ^= 1u; }
         if (++s == S) { s = 0; ph ^= 1u; }
       }
-      if (lane == 0) {
+      if (lane == 0 && mw == 0) {
         PROF_PUT(3, pm_wa); PROF_PUT(4, pm_wt); PROF_PUT(5, pm_wb); PROF_PUT(6, pm_iss); PROF_PUT(7, pm_n);
         PROF_PUT(24, PROF_NOW() - pm_start);
       }
-      {
+      if (mw == 0) {
         // the elected lane's private counters (max over lanes: the others hold 0)
         PROF_PUT(25, __reduce_max_sync(0xffffffffu, (unsigned)pm_f)); PROF_PUT(26, __reduce_max_sync(0xffffffffu, (unsigned)pm_m));
         PROF_PUT(27, __reduce_max_sync(0xffffffffu, (unsigned)pm_c));
@@ -558,7 +560,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     __syncwarp();
   } else if (warp == kWarpWeights) {
     // ===================== weight loader =====================
-    uint8_t *sched = sched_all + 1 * kMaxK;
+    uint8_t *sched = sched_all + 1 * sched_stride;
     const uint32_t b_base = smem_u32(b_ring);
     Ring br;
     for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
@@ -567,16 +569,25 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
       for (int k = 0; k < p.K; ++k) {
         if (!sched[k]) continue;
         for (int ch = 0; ch < p.nchunk; ++ch) {
-          mbar_wait_warp(&b_empty[br.stage], br.phase ^ 1u);
+          // merged ring: the image rides on the stage's own barriers (one wait and one
+          // commit less per stage on the MMA warps, whose dependent chain bounds the kernel)
+          uint64_t *empty = p.b_merged ? &a_empty[br.stage] : &b_empty[br.stage];
+          uint64_t *full = p.b_merged ? &a_full[br.stage] : &b_full[br.stage];
+          mbar_wait_warp(empty, br.phase ^ 1u);
           if (lane == 0) {
             const uint8_t *src = (const uint8_t *)p.bpack + (((size_t)sp * p.K + k) * p.nchunk + ch) * b_bytes;
-            mbar_arrive_expect_tx(&b_full[br.stage], b_bytes);
-            bulk_g2s(b_base + br.stage * b_bytes, src, b_bytes, &b_full[br.stage]);
+            mbar_arrive_expect_tx(full, b_bytes);
+            bulk_g2s(b_base + br.stage * b_bytes, src, b_bytes, full);
           }
           __syncwarp();
-          br.advance(kBStages);
+          br.advance(p.b_merged ? S : kBStages);
         }
       }
+    }
+    if (p.b_merged) {
+      // the stage that carries the END ticket counts an arrival of this warp as well
+      mbar_wait_warp(&a_empty[br.stage], br.phase ^ 1u);
+      if (lane == 0) mbar_arrive(&a_full[br.stage]);
     }
   }
 
@@ -602,7 +613,7 @@ static int arm_hang_report() {
 }
 
 struct TCPlan {
-  int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots;
+  int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots, b_merged;
   size_t smem, bpack_bytes, mask_bytes;
 };
 
@@ -627,14 +638,27 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   if (const char *e = getenv("MK_TC_ISLOTS")) pl.i_slots = std::max(4, std::min(kMaxIdxSlots, atoi(e) & ~3));
   pl.W = (K + 31) / 32;
   const size_t b_bytes = (size_t)pl.NT * 128;
-  const size_t fixed = 1024 /*align slack*/ + pl.b_stages * b_bytes + (size_t)pl.i_slots * pl.T * kTileM * 4 +
-                       kSchedCopies * kMaxK + 64 + 1024 /*barriers*/;
+  size_t fixed = 1024 /*align slack*/ + pl.b_stages * b_bytes + (size_t)pl.i_slots * pl.T * kTileM * 4 +
+                 kSchedCopies * (size_t)((K + 31) & ~31) + 64 + 1024 /*barriers*/;
   const size_t budget = 227 * 1024;
   const size_t stage_bytes = (size_t)pl.T * kTileBytes;
   int S = (int)((budget - fixed) / stage_bytes);
   S = std::min(S, 12);   // tickets[] holds 16
   if (S < 3 || S * pl.T <= 4) return false;   // producer teams: consecutive stages of a team must be < S apart
   pl.a_stages = S;
+  // Whatever is left after the A ring goes to the weight ring: with two images the copy of
+  // the image for stage n+2 starts when stage n retires, one stage period before it is
+  // needed, and the MMA warps wait for it (10 % of their time at 64 -> 64, -DMK_TC_PROF).
+  // If there is room for one weight image per A stage, the weight ring is merged into the A
+  // ring: image and gathered tiles of a stage share the stage's full / empty barriers.
+  pl.b_merged = 0;
+  if (!getenv("MK_TC_BSTAGES")) {
+    while (pl.b_stages < S && pl.b_stages < kMaxBStages && fixed + b_bytes + (size_t)S * stage_bytes <= budget) {
+      ++pl.b_stages;
+      fixed += b_bytes;
+    }
+    pl.b_merged = (pl.b_stages == S && !getenv("MK_TC_NOMERGE")) ? 1 : 0;
+  }
   pl.smem = fixed + (size_t)S * stage_bytes;
   pl.bpack_bytes = align256s((size_t)nsplit * K * pl.nchunk * b_bytes);
   pl.mask_bytes = align256s((size_t)((n_out + kTileM - 1) / kTileM) * pl.W * 4);
@@ -686,7 +710,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y; p.out_rows = out_rows;
   p.ld = ld; p.n_out = n_out; p.n_in = n_in; p.K = K; p.W = pl.W; p.kflip = kflip;
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
-  p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots;
+  p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots; p.b_merged = pl.b_merged;
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);

@@ -24,20 +24,26 @@ tin = abi.insert(c)
 nbr, ld, counts = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offsets3())
 x = torch.randn(n, 64).bfloat16().cuda()
 w = (torch.randn(27, 64, 64) / 40).bfloat16().cuda()
-mask = abi.tile_mask(nbr, n, ld, 27)
+perm, nbr_o = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])   # the product layout
+mask_o = abi.tile_mask(nbr_o, n, ld, 27)
 names = {0: "epi wait t_full", 1: "epi work", 2: "idx wait i_empty", 3: "mma wait a_full", 4: "mma wait t_empty",
          5: "mma wait b_full", 6: "mma issue", 7: "mma stages", 24: "mma total", 25: "mma: proxy fence", 26: "mma: umma issue",
          27: "mma: commits"}
 for t in range(4):
     names.update({8 + 4 * t: f"team{t} wait a_empty", 9 + 4 * t: f"team{t} wait i_full", 10 + 4 * t: f"team{t} issue",
                   11 + 4 * t: f"team{t} tiles"})
-for cfg in sys.argv[1:] or ["4,2,4"]:
-    T_, B_, I_ = cfg.split(",")
-    os.environ["MK_TC_T"], os.environ["MK_TC_BSTAGES"], os.environ["MK_TC_ISLOTS"] = T_, B_, I_
+for cfg in sys.argv[1:] or ["default"]:
+    if cfg == "default":     # the plan's own choices
+        T_ = B_ = I_ = "-"
+        for k_ in ("MK_TC_T", "MK_TC_BSTAGES", "MK_TC_ISLOTS"):
+            os.environ.pop(k_, None)
+    else:
+        T_, B_, I_ = cfg.split(",")
+        os.environ["MK_TC_T"], os.environ["MK_TC_BSTAGES"], os.environ["MK_TC_ISLOTS"] = T_, B_, I_
     for _ in range(3):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        abi.conv_fwd(x, w, nbr, ld, n, mask=mask)
+        abi.conv_fwd_rows(x, w, nbr_o, ld, n, perm, mask=mask_o)
         b.record()
         torch.cuda.synchronize()
     buf = np.zeros(148 * 32, np.uint64)
