@@ -82,6 +82,7 @@ struct ConvTCParams {
   const int32_t *out_rows; // optional [n_out]: table column o is output row out_rows[o] (tile-ordered maps)
   int64_t ld, n_out, n_in;
   int K, W, kflip;
+  int *group_counter;     // optional [gridDim.y], zeroed before the launch: groups are handed out in order, on demand
   int b_merged;           // weight ring = A ring (same depth): image s travels with stage s on the stage's barriers
   int c_in, c_out, nchunk, NT, T;
   int a_stages, b_stages, i_slots;
@@ -107,7 +108,9 @@ struct Ring {
 //   transpose == 1: B(n, c) = W[k][n0 + n][c]        W: [K, c_n, c_red]
 template <typename T>
 __global__ void k_pack_b(const T *__restrict__ w, int transpose, int K, int c_red, int c_n, int nchunk, int NT,
-                         int nsplit, T *__restrict__ out) {
+                         int nsplit, T *__restrict__ out, int *__restrict__ group_counter) {
+  // (also resets the forward kernel's group counters: it runs right before it on the stream)
+  if (group_counter && blockIdx.x == 0 && (int)threadIdx.x < nsplit) group_counter[threadIdx.x] = 0;
   const int64_t total = (int64_t)nsplit * K * nchunk * NT * 64;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
        e += (int64_t)gridDim.x * blockDim.x) {
@@ -181,6 +184,50 @@ __device__ __forceinline__ uint32_t fill_sched(uint8_t *sched, const ConvTCParam
   return __reduce_add_sync(0xffffffffu, cnt);   // number of offsets with any neighbour in the group
 }
 
+// Queue through which the index warp tells the other roles which group comes next (dynamic
+// group scheduling).  One claim per group: the cost is a handful of barrier operations per
+// ~40 k cycles of work.  Every consumer warp waits on every phase of `full`, the producer on
+// every phase of `empty` (parity-wait soundness).
+constexpr int kGroupQ = 4;
+constexpr int kGroupConsumers = 4 /*epilogue*/ + 1 /*weights*/ + kGatherWarps;
+struct GroupQueue {
+  int *q;
+  uint64_t *full, *empty;
+  int *counter;   // nullptr: static schedule (every gridDim.x-th group)
+  int ngroups;
+  uint32_t slot = 0, phase = 0;
+  __device__ __forceinline__ int fetch(bool producer, int lane) {
+    int g = 0;
+    if (producer) {
+      mbar_wait_warp(&empty[slot], phase ^ 1u);
+      if (lane == 0) {
+        g = atomicAdd(counter, 1);
+        if (g >= ngroups) g = -1;
+        *(volatile int *)&q[slot] = g;
+        mbar_arrive(&full[slot]);   // release: orders the entry before the phase completes
+      }
+      g = __shfl_sync(0xffffffffu, g, 0);
+    } else {
+      if (lane == 0) mbar_wait_shared(&full[slot], phase);   // two dozen waiters: short polls (no sleeping wait)
+      __syncwarp();
+      g = *(volatile int *)&q[slot];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+    }
+    if (++slot == kGroupQ) { slot = 0; phase ^= 1u; }
+    return g;
+  }
+  __device__ __forceinline__ int first(bool producer, int lane) {
+    if (counter) return fetch(producer, lane);
+    return (int)blockIdx.x < ngroups ? (int)blockIdx.x : -1;
+  }
+  __device__ __forceinline__ int next(bool producer, int lane, int g) {
+    if (counter) return fetch(producer, lane);
+    g += (int)gridDim.x;
+    return g < ngroups ? g : -1;
+  }
+};
+
 // Ticket: what the MMA warp has to do with one A stage (= the T gathered tiles of
 // one offset and channel chunk), written by a gather team (the teams walk the
 // schedule anyway; the MMA warp is the serial resource of the CTA and must not).
@@ -210,18 +257,29 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   uint64_t *b_full = a_empty + S, *b_empty = b_full + kBStages;
   uint64_t *i_full = b_empty + kBStages, *i_empty = i_full + kIdxSlots;
   uint64_t *t_full = i_empty + kIdxSlots, *t_empty = t_full + 2;
-  uint32_t *tmem_slot = (uint32_t *)(t_empty + 2);
+  uint64_t *gq_full = t_empty + 2, *gq_empty = gq_full + kGroupQ;
+  uint32_t *tmem_slot = (uint32_t *)(gq_empty + kGroupQ);
+  int *gq = (int *)(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (p.n_out + kTileM - 1) / kTileM;
+  const bool role_is_idx = warp == kWarpIdx;
   const int sp = blockIdx.y;
   const int acc_stride = (p.NT + 31) & ~31;
+  // Which groups this CTA works on.  Static: every gridDim.x-th group.  Dynamic (group_counter):
+  // the index warp claims the next group of the layer when its prefetch gets there and
+  // publishes it to the other roles through a small queue (gq); groups are still handed
+  // out in table order, so concurrently processed groups stay neighbours in L2, but a CTA
+  // that drew cheap groups simply takes more of them (static: the slowest CTA of the
+  // north-star layer carried 9 % more stages than the mean).
+  GroupQueue gq_ctl{gq, gq_full, gq_empty, p.group_counter ? p.group_counter + blockIdx.y : nullptr, p.ngroups};
 
   if (threadIdx.x == 0) {
     for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u + (p.b_merged ? 1u : 0u)); mbar_init(&a_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
     for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], kMmaWarps); mbar_init(&t_empty[s], 4); }
+    for (int s = 0; s < kGroupQ; ++s) { mbar_init(&gq_full[s], 1); mbar_init(&gq_empty[s], kGroupConsumers); }
     fence_barrier_init();
   }
   if (warp == kWarpMma0) tmem_alloc_512(tmem_slot);
@@ -234,7 +292,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     // ===================== epilogue =====================
     uint32_t it = 0;   // counts the groups that have any work (the others never reach the MMA thread)
     PROF_DECL(pe_wait = 0, pe_work = 0, pe_t0 = 0, pe_t1 = 0;)
-    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+    for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
       const uint32_t h = it & 1u;
       const int64_t tile0 = (int64_t)g * p.T;
       uint32_t any = 0;
@@ -298,7 +356,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     const uint32_t i_base = smem_u32(idx_ring);
     Ring ir;
     PROF_DECL(pi_wait = 0, pi_t0 = 0;)
-    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+    for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
       const int64_t tile0 = (int64_t)g * p.T;
       fill_sched(sched, p, tile0, ntiles, lane);
       for (int k = 0; k < p.K; ++k) {
@@ -363,7 +421,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     uint32_t nst = 0;                              // stages so far
     uint32_t it = 0;                               // groups with work so far
     PROF_DECL(pg_we = 0, pg_wi = 0, pg_iss = 0, pg_t0 = 0, pg_n = 0;)
-    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+    for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
       const int64_t tile0 = (int64_t)g * p.T;
       const uint32_t n_stages = fill_sched(sched, p, tile0, ntiles, lane) * nchunk;
       if (!n_stages) continue;
@@ -563,7 +621,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     uint8_t *sched = sched_all + 1 * sched_stride;
     const uint32_t b_base = smem_u32(b_ring);
     Ring br;
-    for (int g = blockIdx.x; g < p.ngroups; g += gridDim.x) {
+    for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
       const int64_t tile0 = (int64_t)g * p.T;
       fill_sched(sched, p, tile0, ntiles, lane);
       for (int k = 0; k < p.K; ++k) {
@@ -614,7 +672,7 @@ static int arm_hang_report() {
 
 struct TCPlan {
   int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots, b_merged;
-  size_t smem, bpack_bytes, mask_bytes;
+  size_t smem, bpack_bytes, mask_bytes, range_bytes;
 };
 
 static inline size_t align256s(size_t b) { return (b + 255) & ~(size_t)255; }
@@ -662,6 +720,7 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   pl.smem = fixed + (size_t)S * stage_bytes;
   pl.bpack_bytes = align256s((size_t)nsplit * K * pl.nchunk * b_bytes);
   pl.mask_bytes = align256s((size_t)((n_out + kTileM - 1) / kTileM) * pl.W * 4);
+  pl.range_bytes = 256;   // group counters, one int per output split
   return true;
 }
 
@@ -673,7 +732,7 @@ bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) 
 int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
   TCPlan pl;
   if (!make_plan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return 0;
-  return (int64_t)(pl.bpack_bytes + pl.mask_bytes + 256);
+  return (int64_t)(pl.bpack_bytes + pl.mask_bytes + pl.range_bytes + 256);
 }
 
 int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint32_t *mask, cudaStream_t st) {
@@ -693,11 +752,13 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   uint8_t *ws = (uint8_t *)workspace;
   T *bpack = (T *)ws;
   uint32_t *mask = (uint32_t *)(ws + pl.bpack_bytes);
+  // group counters (one per output split) behind the mask; development switch MK_TC_STATIC
+  int *group_counter = getenv("MK_TC_STATIC") ? nullptr : (int *)(ws + pl.bpack_bytes + pl.mask_bytes);
   {
     const int64_t total = (int64_t)pl.nsplit * K * pl.nchunk * pl.NT * 64;
     const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 8);
     k_pack_b<T><<<blocks, 256, 0, st>>>((const T *)w, transpose_w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit,
-                                        bpack);
+                                        bpack, group_counter);
     MK_LAUNCH_CHECK();
   }
   if (tile_mask == nullptr) {
@@ -710,7 +771,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.bpack = bpack; p.nbr = nbr; p.mask = tile_mask; p.y = y; p.out_rows = out_rows;
   p.ld = ld; p.n_out = n_out; p.n_in = n_in; p.K = K; p.W = pl.W; p.kflip = kflip;
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
-  p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots; p.b_merged = pl.b_merged;
+  p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots; p.b_merged = pl.b_merged; p.group_counter = group_counter;
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
