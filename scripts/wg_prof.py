@@ -24,7 +24,8 @@ tin = abi.insert(c)
 nbr, ld, counts = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offsets3())
 x = torch.randn(n, 64).bfloat16().cuda()
 dy = torch.randn(n, 64).bfloat16().cuda()
-mask = abi.tile_mask(nbr, n, ld, 27)
+perm, nbr_o = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])   # the product layout
+mask_o = abi.tile_mask(nbr_o, n, ld, 27)
 names = {0: "mma wait b_full", 1: "mma wait a_full", 2: "mma issue", 3: "mma loop total", 4: "team0 in-panel block", 5: "team0 tile sched"}
 for t in range(4):
     names.update({8 + 4 * t: f"team{t} wait i_full", 9 + 4 * t: f"team{t} wait a_empty", 10 + 4 * t: f"team{t} issue",
@@ -34,7 +35,7 @@ for kn in sys.argv[1:] or ["0"]:
     for _ in range(3):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        abi.conv_wgrad(x, dy, nbr, ld, n, 27, mask=mask)
+        abi.conv_wgrad(x, dy, nbr_o, ld, n, 27, mask=mask_o, dy_rows=perm)
         b.record()
         torch.cuda.synchronize()
     buf = np.zeros(148 * 32, np.uint64)
@@ -45,3 +46,8 @@ for kn in sys.argv[1:] or ["0"]:
     for k in sorted(names):
         v = buf[:, k]
         print(f"  {names[k]:22s} {v.mean() / 1e3:10.1f}  (min {v.min() / 1e3:.1f} max {v.max() / 1e3:.1f})")
+    # loop total per pair group (blockIdx.y = the two halves of buf) and its spread over the tile splits
+    tot = buf[:, 3].reshape(2, -1) / 1e3
+    for y in range(2):
+        print(f"  pair group {y}: mma loop total mean {tot[y].mean():.1f} min {tot[y].min():.1f} max {tot[y].max():.1f}; "
+              f"first 12 splits {np.round(tot[y][:12], 0)}")
