@@ -80,7 +80,7 @@ def _inv_mask(mgr, km: _KernelMap) -> torch.Tensor:
 def _tile_order_cfg():
     import os
     return (os.environ.get("MK_TILE_ORDER", "1") != "0", int(os.environ.get("MK_TILE_ORDER_MIN", "65536")),
-            int(os.environ.get("MK_TILE_ORDER_BLOCK", "7")))
+            int(os.environ.get("MK_TILE_ORDER_BLOCK", "8")))
 
 
 def _order_table(mgr, table, n_rows, ld, K, coords):
