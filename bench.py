@@ -381,9 +381,9 @@ def run_engine(args):
             "roofline": {"bound": "tensor", "kernel": "conv forward (%s)" % ("tcgen05" if conv_path else "simt"),
                          "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
                          # dram__bytes_read+write of one k_conv_tc launch at R=271 on the tile-ordered table,
-                         # ncu --set full (profiles/r1e_ncu_full_conv_final.csv); algorithmic bytes
+                         # ncu --set full (profiles/r1f_ncu_full_conv_final.csv); algorithmic bytes
                          # are x + y + neighbour table + output-row permutation
-                         "traffic": 306.6e6 if (conv_path and R == R_FULL) else None,
+                         "traffic": 306.0e6 if (conv_path and R == R_FULL) else None,
                          "alg_bytes_per_launch": int(n * (C_IN + C_OUT) * 2 + 4 * KS ** 3 * n + 4 * n),
                          "peak_source": pk["source"] + " (sustained bf16: kernel timed inside the step loop)",
                          "useful_flops_per_launch": flops_pass},

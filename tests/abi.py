@@ -104,7 +104,7 @@ def tc_eligible(dtype, n_rows, K, c_in, c_out):
     return bool(_lib.load().mk_conv_tc_eligible(DT[dtype], n_rows, K, c_in, c_out))
 
 
-def tile_order(nbr, n_rows, ld, K, coords_dev=None, block_log2=7):
+def tile_order(nbr, n_rows, ld, K, coords_dev=None, block_log2=8):
     """(order [n_rows], table in tile order [K, ld])"""
     lib = _lib.load()
     order = torch.empty(max(n_rows, 1), dtype=torch.int32, device="cuda")
