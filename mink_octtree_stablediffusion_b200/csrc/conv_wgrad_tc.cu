@@ -486,14 +486,30 @@ done_role:
   }
 }
 
-// dw[e] = sum over the X partials, fixed order
+// dw[e] = sum over the X partials in a fixed order (deterministic): warp w of a block sums
+// the partials s = w, w + 8, ... of 32 consecutive float4 columns (coalesced 512-byte rows,
+// eight independent chains in flight per column instead of one of X dependent loads), then
+// warp 0 adds the eight sums in order.
 template <typename T>
-__global__ void k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t n, T *__restrict__ dw) {
-  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (i >= n) return;
+__global__ void __launch_bounds__(256)
+k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t n, T *__restrict__ dw) {
+  __shared__ float4 part[8][32];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t i = ((int64_t)blockIdx.x * 32 + lane) * 4;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int s = 0; s < X; ++s) {
-    const float4 v = __ldg(reinterpret_cast<const float4 *>(partial + (size_t)s * n + i));
+  if (i < n) {
+#pragma unroll 4
+    for (int s = w; s < X; s += 8) {
+      const float4 v = __ldg(reinterpret_cast<const float4 *>(partial + (size_t)s * n + i));
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  part[w][lane] = acc;
+  __syncthreads();
+  if (w != 0 || i >= n) return;
+#pragma unroll
+  for (int j = 1; j < 8; ++j) {
+    const float4 v = part[j][lane];
     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
   }
   dw[i] = from_acc<T, float>(acc.x);
@@ -622,7 +638,7 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_ro
   k_conv_wgrad_tc<<<grid, kThreads, pl.smem, st>>>(p, tmap_dy, tmap_dy_row);
   MK_LAUNCH_CHECK();
   const int64_t n_w = (int64_t)K * c_in * c_out;
-  const unsigned blocks = (unsigned)ceil_div(n_w / 4, 256);
+  const unsigned blocks = (unsigned)ceil_div(n_w / 4, 32);
   if (dtype == MK_BF16)
     k_wgrad_reduce<__nv_bfloat16><<<blocks, 256, 0, st>>>(partial, pl.X, n_w, (__nv_bfloat16 *)dw);
   else
