@@ -24,8 +24,10 @@
 
 namespace mk {
 
-// key = [hash16(batch, x>>b, y>>b, z>>b) | pattern : 32], 48 significant bits = six
-// 8-bit passes of the radix sort instead of eight.  Rows of one block always share
+constexpr int kBlockBits = 13;
+
+// key = [hash13(batch, x>>b, y>>b, z>>b) | pattern : min(K, 32)]: 40 significant bits at
+// K = 27 = five 8-bit passes of the radix sort instead of eight.  Rows of one block always share
 // the hash; distinct blocks that collide merely share tiles where their patterns
 // agree, which costs a little locality and nothing else.  pattern = bit k set iff
 // nbr[k, row] >= 0 (first 32 offsets), sorted by its rank in the Gray sequence.
@@ -42,14 +44,14 @@ __global__ void k_order_key(const int32_t *__restrict__ nbr, int64_t n, int64_t 
     const int32_t *c = coords + r * ncols;
     blk = (uint32_t)__ldg(c) * 0x9E3779B1u;
     for (int d = 1; d < ncols; ++d) blk = (blk ^ (uint32_t)(__ldg(c + d) >> bl)) * 0x85EBCA6Bu;
-    blk = (blk ^ (blk >> 15)) & 0xFFFFu;
+    blk = (blk ^ (blk >> 15)) & ((1u << kBlockBits) - 1u);
   }
   // rank of the pattern along the reflected Gray sequence: neighbours in the sorted order
   // differ in one offset, so a tile that straddles several patterns touches fewer offsets
   // than in plain binary order (126 k -> 122.5 k non-empty (tile, offset) pairs at 1 M voxels)
   uint32_t gr = pat;
   gr ^= gr >> 1; gr ^= gr >> 2; gr ^= gr >> 4; gr ^= gr >> 8; gr ^= gr >> 16;
-  keys[r] = ((unsigned long long)blk << 32) | gr;
+  keys[r] = ((unsigned long long)blk << kk) | gr;
   rows[r] = (int32_t)r;
 }
 
@@ -63,7 +65,6 @@ __global__ void k_permute_table(const int32_t *__restrict__ src, const int32_t *
     dst[(int64_t)k * ld + slot] = r >= 0 ? __ldg(src + (int64_t)k * ld + r) : -1;
 }
 
-constexpr int kKeyBits = 48;
 
 static inline size_t align256o(size_t b) { return (b + 255) & ~(size_t)255; }
 
@@ -105,7 +106,7 @@ extern "C" int mk_kmap_tile_order(const int32_t *nbr, int64_t n_rows, int64_t ld
     k_order_key<<<(unsigned)((n_rows + 255) / 256), 256, 0, st>>>(nbr, n_rows, ld, K, coords, ncols, block_log2,
                                                                    keys_in, rows_in);
     MK_LAUNCH_CHECK();
-    MK_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, rows_in, order, (int)n_rows, 0, kKeyBits,
+    MK_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, rows_in, order, (int)n_rows, 0, (K < 32 ? K : 32) + kBlockBits,
                                             st));
   }
   k_permute_table<<<(unsigned)((ld + 255) / 256), 256, 0, st>>>(nbr, order, n_rows, ld, K, nbr_ordered);
