@@ -61,8 +61,16 @@ __global__ void k_permute_table(const int32_t *__restrict__ src, const int32_t *
   const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= ld) return;
   const int64_t r = slot < n ? (int64_t)__ldg(order + slot) : -1;
-  for (int k = 0; k < K; ++k)
-    dst[(int64_t)k * ld + slot] = r >= 0 ? __ldg(src + (int64_t)k * ld + r) : -1;
+  // nine independent loads in flight per thread (each is a 32-byte sector for 4 useful bytes:
+  // the pass is bound by L2 sector throughput and by latency, not by HBM)
+  for (int k0 = 0; k0 < K; k0 += 9) {
+    int32_t v[9];
+#pragma unroll
+    for (int j = 0; j < 9; ++j) v[j] = (r >= 0 && k0 + j < K) ? __ldg(src + (int64_t)(k0 + j) * ld + r) : -1;
+#pragma unroll
+    for (int j = 0; j < 9; ++j)
+      if (k0 + j < K) dst[(int64_t)(k0 + j) * ld + slot] = v[j];
+  }
 }
 
 
