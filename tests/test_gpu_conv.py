@@ -245,6 +245,45 @@ def test_tensor_core_wide_channels(cin, cout):
             assert err <= 1e-2, (ordered, err)
 
 
+@pytest.mark.parametrize("cin,cout", [(32, 64), (64, 128)])
+def test_tensor_core_5x5x5(cin, cout):
+    """5^3 kernel (K = 125: four mask words per tile, eight interleaved pair groups in the weight
+    gradient, a 45-bit tile-order key) on the tensor-core path, plain and tile-ordered table,
+    against the fp32 CUDA-core path."""
+    c = _northstar_cloud(40, "shuffled")
+    offs = O.kernel_offsets([5, 5, 5], [1, 1, 1])
+    K = len(offs)
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    assert abi.tc_eligible(torch.bfloat16, n, K, cin, cout)
+    perm, nbr_t = abi.tile_order(nbr, n, ld, K, tin["coords_dev"])
+    assert np.array_equal(np.sort(perm.cpu().numpy()), np.arange(n))
+    g = torch.Generator().manual_seed(17)
+    x = torch.randn(n, cin, generator=g).bfloat16().cuda()
+    dy = torch.randn(n, cout, generator=g).bfloat16().cuda()
+    w = (torch.randn(K, cin, cout, generator=g) / (K * cin) ** 0.5).bfloat16().cuda()
+    abi.force_simt(1)
+    try:
+        xf, dyf, wf = x.float(), dy.float(), w.float()
+        ref = (abi.conv_fwd(xf, wf, nbr, ld, n), abi.conv_fwd(dyf, wf, nbr, ld, n, transpose_w=1, kflip=1),
+               abi.conv_wgrad(xf, dyf, nbr, ld, n, K))
+    finally:
+        abi.force_simt(0)
+    for ordered in (False, True):
+        if ordered:
+            got = (abi.conv_fwd_rows(x, w, nbr_t, ld, n, perm),
+                   abi.conv_fwd_rows(dy, w, nbr_t, ld, n, perm, transpose_w=1, kflip=1),
+                   abi.conv_wgrad(x, dy, nbr_t, ld, n, K, dy_rows=perm))
+        else:
+            got = (abi.conv_fwd(x, w, nbr, ld, n), abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1),
+                   abi.conv_wgrad(x, dy, nbr, ld, n, K))
+        assert abi.last_path() == 1
+        for u, r in zip(got, ref):
+            err = float((u.float() - r).abs().max() / r.abs().max())
+            assert err <= 1e-2, (ordered, err)
+
+
 def test_tensor_core_plans_agree_under_load(monkeypatch):
     """Regression for a pipeline race of the forward/dgrad kernel: with fewer than four tiles
     per group the A ring is deeper than the neighbour-index ring, and a gather team whose tile
