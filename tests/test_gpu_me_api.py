@@ -88,6 +88,42 @@ def test_strided_conv_and_transpose_roundtrip_keys():
     assert np.abs(u.F.detach().double().cpu().numpy() - ref).max() <= 1e-5 * np.abs(ref).max()
 
 
+def test_tile_ordered_strided_and_transposed_maps(monkeypatch):
+    """The tile-ordered table on maps that are not symmetric (stride 2 down, k2 s2 transposed
+    up, and their data gradients through the ordered INVERSE table): a bf16 encoder/decoder pair
+    through the ME API with the ordering forced on (MK_TILE_ORDER_MIN = 0) must give what it
+    gives with the ordering off - features and input gradient bit-identical (a row's sum does
+    not depend on its tile), weight gradients within the bf16 tolerance."""
+    ME = _me()
+    c = O.sphere_surface(40, 5)
+    torch.manual_seed(4)
+    f0 = torch.randn(len(c), 32).bfloat16()
+    w_down = (torch.randn(27, 32, 64) / 30).bfloat16()
+    w_up = (torch.randn(8, 64, 32) / 20).bfloat16()
+
+    def run(order_on):
+        monkeypatch.setenv("MK_TILE_ORDER", "1" if order_on else "0")
+        monkeypatch.setenv("MK_TILE_ORDER_MIN", "0")
+        f = f0.clone().cuda().requires_grad_(True)
+        st = ME.SparseTensor(f, torch.from_numpy(c).cuda())
+        down = ME.MinkowskiConvolution(32, 64, kernel_size=3, stride=2, dimension=3).cuda().to(torch.bfloat16)
+        up = ME.MinkowskiConvolutionTranspose(64, 32, kernel_size=2, stride=2, dimension=3).cuda().to(torch.bfloat16)
+        with torch.no_grad():
+            down.kernel.copy_(w_down.cuda())
+            up.kernel.copy_(w_up.cuda())
+        u = up(down(st))
+        g = torch.Generator().manual_seed(9)
+        dy = torch.randn(u.F.shape, generator=g).bfloat16().cuda()
+        (u.F * dy).sum().backward()
+        return u.F.detach(), f.grad.detach(), down.kernel.grad.detach(), up.kernel.grad.detach()
+
+    off = run(False)
+    on = run(True)
+    assert torch.equal(on[0], off[0]) and torch.equal(on[1], off[1])
+    for a, b in ((on[2], off[2]), (on[3], off[3])):
+        assert float((a.float() - b.float()).abs().max() / b.float().abs().max()) <= 1e-2
+
+
 def test_generative_transpose_then_pruning_octree_step():
     """One octree decoder level (modules/vae_block.py:279-296, examples/ae_res.py:556-609)."""
     ME = _me()
