@@ -39,6 +39,12 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t by
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+// Suspend-time hint of the sleeping waits.  A sleeper occasionally misses its wake-up (seen
+// as one launch in ~15 000 taking 2 ms longer with the former 10 ms hint: the last waiter of a
+// CTA, with no further barrier event to wake it, slept until the hardware's limit); with
+// 20 us the same event costs at most a few microseconds and ordinary waits (well under the
+// hint) are unchanged.
+constexpr uint32_t kSuspendHintNs = 20000u;
 // Potentially-blocking test of a phase: the suspend-time hint lets the hardware
 // park the thread until the phase completes instead of busy-polling.  (A bare
 // try_wait/test_wait loop in two dozen warps eats the issue slots of the warps
@@ -50,7 +56,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(kSuspendHintNs)
       : "memory");
   return ok != 0;
 }
@@ -170,7 +176,7 @@ __device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity), "r"(0x989680u)
+      : "r"(bar), "r"(parity), "r"(kSuspendHintNs)
       : "memory");
   return ok != 0;
 }
