@@ -116,6 +116,18 @@ int64_t mk_select_workspace_bytes(int64_t n);
 /* kept[j] = index of the j-th non-zero keep byte (order preserved) */
 int mk_select_flagged(const uint8_t *keep, int64_t n, int32_t *kept,
                       void *workspace, int64_t *n_kept_dev, void *stream);
+/* mk_select_flagged for callers that cannot allocate (CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in
+ * the reference.  Same result as
+ * mk_select_flagged, but the scan scratch is a fixed static __device__ array
+ * inside the library (33 KB per GPU that loads it, held until exit) instead of
+ * a caller workspace; the call performs no cudaMalloc / cudaFree and calls no
+ * allocating routine.  n > mk_select_static_max_rows() (16 777 216) is rejected
+ * with MK_EINVAL.  Every call on a device shares that one array: calls that
+ * overlap on the GPU (different streams) race; serialise them on one stream. */
+int64_t mk_select_static_max_rows(void);
+int mk_select_flagged_static(const uint8_t *keep, int64_t n, int32_t *kept,
+                             int64_t *n_kept_dev, void *stream);
 /* dst[j, :] = src[idx[j], :]   (row_bytes per row, any dtype) */
 int mk_rows_gather(const void *src, const int32_t *idx, int64_t n_idx,
                    int64_t row_bytes, void *dst, void *stream);

@@ -37,6 +37,8 @@ PROTOTYPES = {
     "mk_coords_origin": (_i, [_p, _i64, _i, _p, _p]),
     "mk_select_workspace_bytes": (_i64, [_i64]),
     "mk_select_flagged": (_i, [_p, _i64, _p, _p, _p, _p]),
+    "mk_select_static_max_rows": (_i64, []),
+    "mk_select_flagged_static": (_i, [_p, _i64, _p, _p, _p]),
     "mk_rows_gather": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "mk_rows_scatter": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "mk_kmap_build": (_i, [_p, _i64, _i, _p, _i64, _p, _i, _p, _i64, _p, _p]),

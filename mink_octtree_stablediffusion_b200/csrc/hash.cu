@@ -567,6 +567,63 @@ int mk_select_flagged(const uint8_t *keep, int64_t n, int32_t *kept,
   return MK_OK;
 }
 
+// ---------------------------------------------------------------------------
+// mk_select_flagged_static: mk_select_flagged without a caller workspace and
+// without any allocation.  The block-sum scratch is the file-scope device array
+// below (one copy per GPU that loads the library, held until exit).  The array's
+// NAME is only a host-side stand-in in host code; the device address is fetched
+// once per device with cudaGetSymbolAddress (that device current) and cached.
+// Nothing in the scratch has to start at zero: k_flag_count writes every entry
+// [0, nblk) before k_scan_block_sums / k_flag_compact read it, so the previous
+// call's contents are simply overwritten.  All calls share the array: two calls
+// that overlap on the GPU (different streams) race on it.
+constexpr int64_t kStaticSelectMaxBlocks = 8192;
+constexpr int64_t kStaticSelectMaxRows = kStaticSelectMaxBlocks * kScanTile;  // 16 777 216
+static __device__ __align__(256) int32_t g_select_scratch[kStaticSelectMaxBlocks + 64];
+
+constexpr int kMaxDevices = 64;
+static int32_t *g_select_scratch_ptr[kMaxDevices];  // device address per device, or null
+
+int64_t mk_select_static_max_rows(void) { return kStaticSelectMaxRows; }
+
+int mk_select_flagged_static(const uint8_t *keep, int64_t n, int32_t *kept,
+                             int64_t *n_kept_dev, void *stream) {
+  MK_CHECK_ARG(n >= 0, "row count out of range");
+  if (n > kStaticSelectMaxRows) {
+    set_error("mk_select_flagged_static: n = %lld exceeds the static scratch limit of %lld rows; "
+              "use mk_select_flagged with a caller workspace",
+              (long long)n, (long long)kStaticSelectMaxRows);
+    return MK_EINVAL;
+  }
+  MK_CHECK_ARG(n_kept_dev, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    MK_CUDA(cudaMemsetAsync(n_kept_dev, 0, sizeof(int64_t), st));
+    return MK_OK;
+  }
+  MK_CHECK_ARG(keep && kept, "null pointer");
+  int dev = -1;
+  MK_CUDA(cudaGetDevice(&dev));
+  MK_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+  int32_t *block_sums = __atomic_load_n(&g_select_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!block_sums) {
+    void *p = nullptr;
+    MK_CUDA(cudaGetSymbolAddress(&p, g_select_scratch));
+    MK_CHECK_ARG(p != nullptr, "cudaGetSymbolAddress returned null");
+    block_sums = (int32_t *)p;
+    __atomic_store_n(&g_select_scratch_ptr[dev], block_sums, __ATOMIC_RELEASE);
+  }
+  const int64_t nblk = ceil_div(n, kScanTile);
+  k_flag_count<<<(unsigned)nblk, kScanThreads, 0, st>>>(keep, n, block_sums);
+  MK_LAUNCH_CHECK();
+  k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nblk, n_kept_dev);
+  MK_LAUNCH_CHECK();
+  k_flag_compact<<<(unsigned)nblk, kScanThreads, 0, st>>>(keep, n, block_sums,
+                                                          kept);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
 int mk_rows_gather(const void *src, const int32_t *idx, int64_t n_idx,
                    int64_t row_bytes, void *dst, void *stream) {
   return rows_copy(src, idx, n_idx, row_bytes, dst, false,
