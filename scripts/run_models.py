@@ -1,0 +1,130 @@
+"""Development driver: run the reference's unchanged models on the engine (GPU)
+and report errors / step times.  python scripts/run_models.py [vae|unet|minkunet ...] [--res R] [--batch B]"""
+import argparse
+import os
+import sys
+import time
+import traceback
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+from harness import workloads as W
+
+
+def timed(fn, n=3):
+    ts = []
+    for _ in range(n):
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t)
+    return ts
+
+
+def run_vae(a):
+    cfg = W.vae_config(resolution=a.res, batch_size=a.batch)
+    torch.manual_seed(0)
+    model, plm, m = W.load_vae(cfg)
+    plm = plm.cuda()
+    if a.dtype == "bf16":
+        plm = plm.to(torch.bfloat16)
+    plm.train()
+    opt = plm.configure_optimizers()
+    coords = torch.from_numpy(W.batched(W.g3_batch(a.res, a.batch))).cuda()
+    print(f"[vae] res {a.res} batch {a.batch}: {len(coords)} voxels", flush=True)
+    batch = {"coords": coords}
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        loss = plm.training_step(batch, 0)
+        loss.backward()
+        opt.step()
+        return loss
+
+    loss = step()
+    print("[vae] first step loss", float(loss), flush=True)
+    ts = timed(step, a.steps)
+    print("[vae] step times (s):", [round(t, 4) for t in ts], "logged", {k: round(float(v), 5) for k, v in plm._logged.items()})
+
+
+def run_minkunet(a):
+    mu = W.load_minkunet()
+    torch.manual_seed(0)
+    net = mu.MinkUNet34C(3, 20, D=3).cuda()
+    if a.dtype == "bf16":
+        net = net.to(torch.bfloat16)
+    import MinkowskiEngine as ME
+    from oracle import oracle as O
+    c = torch.from_numpy(O.sphere_surface(a.radius, 0, 0)).cuda()
+    f = torch.rand(len(c), 3, device="cuda").to(next(net.parameters()).dtype)
+    labels = torch.randint(0, 20, (len(c),), device="cuda")
+    crit = torch.nn.CrossEntropyLoss()
+    print(f"[minkunet] {len(c)} voxels", flush=True)
+
+    def step():
+        net.zero_grad(set_to_none=True)
+        out = net(ME.SparseTensor(f, c))
+        loss = crit(out.F.float(), labels)
+        loss.backward()
+        return loss
+
+    print("[minkunet] loss", float(step()), flush=True)
+    print("[minkunet] step times (s):", [round(t, 4) for t in timed(step, a.steps)])
+
+
+def run_unet(a):
+    cfg = W.diffusion_config(resolution=a.res, batch_size=a.batch, unet_channel=tuple(a.unet_channel))
+    d = W.load_unet(cfg)
+    import MinkowskiEngine as ME
+    torch.manual_seed(0)
+    unet = d.UNet(cfg.unet_channel, cfg).cuda()
+    if a.dtype == "bf16":
+        unet = unet.to(torch.bfloat16)
+    dt = next(unet.parameters()).dtype
+    # latents: stride-8 coordinates of the G3 shapes
+    from oracle import oracle as O
+    c = W.batched(W.g3_batch(a.res, a.batch))
+    lat = torch.from_numpy(O.stride_coords(c, [8, 8, 8])).cuda()
+    x = ME.SparseTensor(torch.randn(len(lat), 4, device="cuda").to(dt), lat, tensor_stride=8)
+    print(f"[unet] {len(lat)} latent voxels", flush=True)
+    t = torch.randint(0, 1000, (a.batch,), device="cuda")
+    noise = torch.randn(len(lat), 4, device="cuda").to(dt)
+
+    def step():
+        unet.zero_grad(set_to_none=True)
+        out = unet(x, t)
+        loss = torch.nn.functional.mse_loss(out.F, noise)
+        loss.backward()
+        return loss
+
+    print("[unet] loss", float(step()), flush=True)
+    print("[unet] step times (s):", [round(t, 4) for t in timed(step, a.steps)])
+
+
+if __name__ == "__main__":
+    pa = argparse.ArgumentParser()
+    pa.add_argument("which", nargs="*", default=["vae"])
+    pa.add_argument("--res", type=int, default=64)
+    pa.add_argument("--batch", type=int, default=2)
+    pa.add_argument("--steps", type=int, default=3)
+    pa.add_argument("--radius", type=int, default=40)
+    pa.add_argument("--dtype", default="fp32")
+    pa.add_argument("--unet_channel", type=int, nargs=4, default=(4, 320, 640, 960))
+    a = pa.parse_args()
+    rc = 0
+    for w in a.which:
+        try:
+            {"vae": run_vae, "unet": run_unet, "minkunet": run_minkunet}[w](a)
+        except Exception:
+            rc = 1
+            print(f"[{w}] FAILED", flush=True)
+            traceback.print_exc()
+            try:
+                torch.cuda.synchronize()
+            except Exception as e:
+                print("cuda error after failure:", e)
+                break
+    sys.exit(rc)
