@@ -38,7 +38,7 @@ class MinkowskiBroadcastBase(MinkowskiModuleBase):
         MinkowskiModuleBase.__init__(self)
         assert isinstance(operation_type, BroadcastMode)
         self.operation_type = operation_type
-        self.broadcast = MinkowskiBroadcastFunction()
+        self.broadcast = MinkowskiBroadcastFunction
 
     def forward(self, input: SparseTensor, input_glob: SparseTensor):
         assert isinstance(input, SparseTensor)

@@ -30,6 +30,17 @@ def _match_dtype(features: torch.Tensor, kernel: torch.Tensor) -> torch.Tensor:
     return kernel if kernel.dtype == features.dtype else kernel.to(features.dtype)
 
 
+def _autocast(features: torch.Tensor) -> torch.Tensor:
+    """Under `torch.autocast("cuda", dtype=bf16|f16)` (Lightning's `precision="bf16-mixed"`,
+    examples/ae_res.py:1016) the convolution is a matmul-class op: features (and, through
+    `_match_dtype`, the kernel) are cast to the autocast dtype, accumulation stays fp32."""
+    if features.is_cuda and features.is_floating_point() and torch.is_autocast_enabled("cuda"):
+        dt = torch.get_autocast_dtype("cuda")
+        if features.dtype != dt and features.dtype != torch.float64:
+            return features.to(dt)
+    return features
+
+
 class _ConvFunctionBase(Function):
     FWD = BWD = None
 
@@ -133,7 +144,7 @@ class MinkowskiConvolutionBase(MinkowskiModuleBase):
             self.kernel = Parameter(torch.empty(*shape, dtype=torch.float32))
         self.bias = Parameter(torch.empty(1, out_channels, dtype=torch.float32)) if bias else None
         self.convolution_mode = convolution_mode
-        self.conv = MinkowskiConvolutionTransposeFunction() if is_transpose else MinkowskiConvolutionFunction()
+        self.conv = MinkowskiConvolutionTransposeFunction if is_transpose else MinkowskiConvolutionFunction
 
     def forward(self, input: SparseTensor,
                 coordinates: Union[torch.Tensor, CoordinateMapKey, SparseTensor] = None):
@@ -144,7 +155,7 @@ class MinkowskiConvolutionBase(MinkowskiModuleBase):
             outfeat = input.F.mm(_match_dtype(input.F, self.kernel))
         else:
             out_key = _get_coordinate_map_key(input, coordinates, self.kernel_generator.expand_coordinates)
-            outfeat = self.conv.apply(input.F, self.kernel, self.kernel_generator, self.convolution_mode,
+            outfeat = self.conv.apply(_autocast(input.F), self.kernel, self.kernel_generator, self.convolution_mode,
                                       input.coordinate_map_key, out_key, input._manager)
         if self.bias is not None:
             outfeat = outfeat + _match_dtype(outfeat, self.bias)

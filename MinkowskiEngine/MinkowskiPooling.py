@@ -96,7 +96,7 @@ class MinkowskiPoolingBase(MinkowskiModuleBase):
         self.kernel_generator = kernel_generator
         self.pooling_mode = pooling_mode
         self.dimension = dimension
-        self.pooling = MinkowskiLocalPoolingFunction()
+        self.pooling = MinkowskiLocalPoolingFunction
 
     def forward(self, input: SparseTensor,
                 coordinates: Union[torch.IntTensor, CoordinateMapKey, SparseTensor] = None):
@@ -142,7 +142,7 @@ class MinkowskiPoolingTranspose(MinkowskiPoolingBase):
         MinkowskiPoolingBase.__init__(self, kernel_size, stride, dilation, kernel_generator, is_transpose=True,
                                       pooling_mode=PoolingMode.LOCAL_SUM_POOLING, dimension=dimension)
         self.kernel_generator.expand_coordinates = expand_coordinates
-        self.pooling = MinkowskiLocalPoolingTransposeFunction()
+        self.pooling = MinkowskiLocalPoolingTransposeFunction
 
 
 class MinkowskiGlobalPoolingFunction(Function):
@@ -178,7 +178,7 @@ class MinkowskiGlobalPooling(MinkowskiModuleBase):
         super().__init__()
         assert isinstance(mode, PoolingMode), f"Mode must be an instance of PoolingMode. mode={mode}"
         self.pooling_mode = mode
-        self.pooling = MinkowskiGlobalPoolingFunction()
+        self.pooling = MinkowskiGlobalPoolingFunction
 
     def forward(self, input: SparseTensor,
                 coordinates: Union[torch.IntTensor, CoordinateMapKey, SparseTensor] = None):

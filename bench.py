@@ -358,6 +358,19 @@ def run_engine(args):
                  "kmap_pairs_export_ms": float(np.median(kme)), "kmap_tile_order_ms": float(np.median(kto)),
                  "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n)}
 
+    # ---- VAE leg (the other half of BASELINE.json's metric) ---------------------
+    vae = None
+    if not args.no_vae:
+        del st, out, gi, gw, bufs
+        gc.collect()
+        torch.cuda.empty_cache()
+        try:
+            vae = run_vae_leg(args, dist, rank, world, dev, lib, args.vae_steps, args.vae_warmup)
+        except Exception as e:      # the conv line must still be printed
+            vae = {"error": f"{type(e).__name__}: {e}"}
+            if world > 1:
+                raise
+
     # ---- reduce over ranks -----------------------------------------------------
     t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -406,9 +419,118 @@ def run_engine(args):
             line["cpu_baseline"] = {"value": s["n"] / s["step_s"], "unit": UNIT, "cores": s["cores"], "kind": "port",
                                     "sample": f"sphere R=96 ({s['n']} voxels), 3^3 64->64 fp32 fwd+bwd, kernel map "
                                               f"cached, median of 3 (oracle/cpu_ref.c, OpenMP)"}
+        if vae is not None:
+            line["vae"] = vae
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------
+# VAE leg: the reference's unchanged octree VAE (examples/ae_res.py) on the engine
+# ---------------------------------------------------------------------------
+_BUCKETS = (("conv", ("k_conv_", "k_pack_b", "k_wgrad_reduce", "k_split_")),
+            ("kernel_map", ("k_kmap", "k_tile_mask", "k_order_key", "k_permute_table", "k_pairs", "k_radix", "k_child")),
+            ("hash_insert", ("k_insert", "k_first_count", "k_scan_block", "k_compact_first", "k_finalize",
+                             "k_table_clear", "k_lookup", "k_dedup")),
+            ("coords_prune", ("k_coords_", "k_flag_", "k_rows_gather", "k_expand")),
+            ("norm", ("batch_norm", "k_inorm", "k_segment", "k_broadcast", "k_global")),
+            ("optimizer", ("multi_tensor_apply", "Optimizer")),
+            ("sort_unique", ("RadixSort", "DeviceScan", "unique", "DeviceSelect", "DeviceReduce")),
+            ("copies", ("Memcpy", "Memset")))
+
+
+def _bucket(name: str) -> str:
+    for b, keys in _BUCKETS:
+        if any(k in name for k in keys):
+            return b
+    return "elementwise_other"
+
+
+def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
+    """VAE steps/s: the unmodified `VaeModule.training_step` (examples/ae_res.py:817-853; VAE.forward
+    :716-789) + backward + Adam on BASELINE config 2 (batch 16 per GPU @ 128^3 G3 shapes,
+    vae_channel (32,128,512,512,4)).  Per step: coordinates copied from pinned host memory, loss read
+    back by the step itself (`.item()`).  N > 1: the reference's DDP recipe - SyncBatchNorm
+    (ae_res.py:996-997) and a gradient all-reduce; every rank holds its own 16 shapes (weak scaling)."""
+    import torch
+    from harness import workloads as W
+    from mink_octtree_stablediffusion_b200.parallel import allreduce_gradients
+    import MinkowskiEngine as ME
+    res, batch = args.vae_res, args.vae_batch
+    cfg = W.vae_config(resolution=res, batch_size=batch)
+    coords_h = torch.from_numpy(W.batched(W.g3_batch(res, batch, first_index=rank * batch))).pin_memory()
+    n_vox = int(coords_h.shape[0])
+    out = {}
+    for mode in args.vae_dtypes.split(","):
+        torch.manual_seed(0)
+        model, plm, _ = W.load_vae(cfg)
+        if world > 1:
+            model = ME.MinkowskiSyncBatchNorm.convert_sync_batchnorm(model)
+            plm.model = model
+        plm = plm.to(dev)
+        plm.train()
+        opt = plm.configure_optimizers()
+        params = [p for p in plm.parameters() if p.requires_grad]
+        amp = torch.autocast("cuda", dtype=torch.bfloat16, enabled=(mode == "bf16"))
+
+        def step():
+            batch_d = {"coords": coords_h.to(dev, non_blocking=True)}
+            opt.zero_grad(set_to_none=True)
+            with amp:
+                loss = plm.training_step(batch_d, 0)
+            loss.backward()
+            if world > 1:
+                allreduce_gradients(params, average=True)
+            opt.step()
+            return loss
+
+        for _ in range(warmup):
+            loss = step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+        l0 = int(lib.mk_launch_count())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        rec = {"steps_per_s": 1e3 / ms, "ms_per_step": ms, "samples_per_s": batch * world * 1e3 / ms,
+               "voxels_per_s": n_vox * world * 1e3 / ms, "loss": float(loss), "engine_launches_per_step":
+               (int(lib.mk_launch_count()) - l0) // steps}
+        if rank == 0 and not args.no_vae_profile:
+            from torch.profiler import ProfilerActivity, profile as tprofile
+            with tprofile(activities=[ProfilerActivity.CUDA]) as prof:
+                step()
+                torch.cuda.synchronize()
+            split = {}
+            for e in prof.key_averages():
+                if e.device_time_total > 0:
+                    b = _bucket(e.key)
+                    split[b] = split.get(b, 0.0) + e.device_time_total / 1e3
+            busy = sum(split.values())
+            split = {k: round(v, 3) for k, v in sorted(split.items(), key=lambda kv: -kv[1])}
+            split["device_idle_host_gaps"] = round(max(ms - busy, 0.0), 3)
+            rec["stage_ms"] = split
+        out[mode] = rec
+        del plm, model, opt, params
+        torch.cuda.empty_cache()
+    return {"workload": f"examples/ae_res.py VAE training_step + Adam, batch {batch}/GPU @ {res}^3 (G3 shapes), "
+                        f"vae_channel (32,128,512,512,4)", "voxels_per_gpu": n_vox, "scaling": "weak",
+            "h2d_bytes_per_step": int(coords_h.numel() * 4), "steps": steps, "warmup": warmup,
+            "dtypes": {"fp32": "reference default precision", "bf16": "torch.autocast(bf16) = Lightning bf16-mixed"},
+            **out}
 
 
 def main():
@@ -419,6 +541,13 @@ def main():
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--radius", type=int, default=R_FULL, help="sphere radius of the synthetic cloud (271 -> 1 M voxels)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-vae", action="store_true", help="skip the VAE steps/s leg")
+    ap.add_argument("--no-vae-profile", action="store_true")
+    ap.add_argument("--vae-steps", type=int, default=10)
+    ap.add_argument("--vae-warmup", type=int, default=3)
+    ap.add_argument("--vae-res", type=int, default=128)
+    ap.add_argument("--vae-batch", type=int, default=16)
+    ap.add_argument("--vae-dtypes", default="bf16,fp32")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

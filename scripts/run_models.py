@@ -24,6 +24,24 @@ def timed(fn, n=3):
     return ts
 
 
+def profile(step, tag):
+    from torch.profiler import ProfilerActivity, profile as tprofile
+    with tprofile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+        step()
+        torch.cuda.synchronize()
+    ev = prof.key_averages()
+    rows = sorted(((e.device_time_total, e.count, e.key) for e in ev if e.device_time_total > 0 and e.device_type.name == "CUDA"),
+                  reverse=True)
+    tot = sum(r[0] for r in rows)
+    print(f"[{tag}] CUDA kernel time total {tot / 1e3:.2f} ms over {sum(r[1] for r in rows)} launches")
+    for t, n, k in rows[:40]:
+        print(f"  {t / 1e3:9.3f} ms  {n:5d}x  {k[:110]}")
+    cpu = sorted(((e.self_cpu_time_total, e.count, e.key) for e in ev if e.device_type.name == "CPU"), reverse=True)
+    print(f"[{tag}] top CPU ops (self time)")
+    for t, n, k in cpu[:25]:
+        print(f"  {t / 1e3:9.3f} ms  {n:5d}x  {k[:110]}")
+
+
 def run_vae(a):
     cfg = W.vae_config(resolution=a.res, batch_size=a.batch)
     torch.manual_seed(0)
@@ -48,6 +66,8 @@ def run_vae(a):
     print("[vae] first step loss", float(loss), flush=True)
     ts = timed(step, a.steps)
     print("[vae] step times (s):", [round(t, 4) for t in ts], "logged", {k: round(float(v), 5) for k, v in plm._logged.items()})
+    if a.profile:
+        profile(step, "vae")
 
 
 def run_minkunet(a):
@@ -112,6 +132,7 @@ if __name__ == "__main__":
     pa.add_argument("--steps", type=int, default=3)
     pa.add_argument("--radius", type=int, default=40)
     pa.add_argument("--dtype", default="fp32")
+    pa.add_argument("--profile", action="store_true")
     pa.add_argument("--unet_channel", type=int, nargs=4, default=(4, 320, 640, 960))
     a = pa.parse_args()
     rc = 0

@@ -1,0 +1,242 @@
+"""The reference's UNCHANGED networks on the engine: the octree
+VAE (`examples/ae_res.py:711`), the sparse-diffusion UNet (`examples/diffusion.py:89`)
+and MinkUNet34C (`examples/minkunet.py:193`), imported from the staged reference
+files (harness/stage.py), run
+
+  * on CPU tensors over the oracle-backed `*CPU` names (oracle/me_cpu_backend.py,
+    float64) — the replay the GPU runs are compared with; and
+  * on the GPU engine (fp64: graph equality at 1e-9; fp32: north_star's 1e-5 on the
+    loss, looser on gradients that pass through ~40 layers of fp32 round-off).
+
+Every decoder level of the VAE (generative-transpose coordinates, `get_target`
+masks, pruning) is also checked bit-exact against the NumPy restatements, at
+BASELINE config 2's size (batch 16 @ 128^3).
+"""
+import contextlib
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from harness import stage
+from harness import workloads as W
+from oracle import me_cpu_backend as CPUB
+from oracle import oracle as O
+
+pytestmark = pytest.mark.skipif(not stage.is_staged() and not stage.stage(),
+                                reason="reference workload files not staged (run harness/stage.py)")
+
+
+@contextlib.contextmanager
+def default_dtype(dt):
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(dt)
+    try:
+        yield
+    finally:
+        torch.set_default_dtype(old)
+
+
+@contextlib.contextmanager
+def fixed_noise(seed):
+    """torch.randn_like / torch.randn draw from one CPU float64 stream, so that the CPU
+    replay and the GPU run see the same noise (the models call them internally)."""
+    gen = torch.Generator().manual_seed(seed)
+    real_like, real_randn = torch.randn_like, torch.randn
+
+    def randn_like(t, **kw):
+        return real_randn(t.shape, generator=gen, dtype=torch.float64).to(device=t.device, dtype=t.dtype)
+    torch.randn_like = randn_like
+    try:
+        yield
+    finally:
+        torch.randn_like = real_like
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp(min=1e-30))
+
+
+def _vae_pair(res, batch, channels, seed):
+    cfg = W.vae_config(resolution=res, batch_size=batch, vae_channel=channels)
+    torch.manual_seed(seed)
+    with default_dtype(torch.float64):
+        model, plm, mod = W.load_vae(cfg)
+    plm.train()
+    coords = torch.from_numpy(W.batched(W.g3_batch(res, batch)))
+    return cfg, plm, coords
+
+
+def _vae_step(plm, coords, dtype, seed):
+    with default_dtype(dtype), fixed_noise(seed):
+        plm.zero_grad(set_to_none=True)
+        sin_feats_like = coords      # the step builds its own SparseTensor from batch["coords"]
+        loss = plm.training_step({"coords": sin_feats_like}, 0)
+        loss.backward()
+    return loss
+
+
+def _decoder_levels(plm, coords, dtype, seed):
+    """(out_cls, targets, sout) of VAE.forward, as the training step calls it."""
+    import MinkowskiEngine as ME
+    with default_dtype(dtype), fixed_noise(seed), torch.no_grad():
+        sin = ME.SparseTensor(features=torch.ones(len(coords), 1).to(coords.device), coordinates=coords.int())
+        out_cls, targets, sout, means, log_vars, zs = plm(sin, sin.coordinate_map_key)
+    return out_cls, targets, sout
+
+
+def _check_levels(gt, out_cls, targets, sout, training=True):
+    """Every decoder level against the NumPy restatements (examples/ae_res.py:557-707)."""
+    gt = np.ascontiguousarray(gt)
+    k2 = O.kernel_offsets([2, 2, 2], [1, 1, 1])
+    C = [t.C.cpu().numpy() for t in out_cls]
+    Fv = [t.F.detach().float().cpu().numpy().reshape(-1) for t in out_cls]
+    strides = [t.tensor_stride[0] for t in out_cls]
+    assert strides == [8, 4, 2, 1]
+    assert np.array_equal(O.canonical_coords(C[0]), O.canonical_coords(O.stride_coords(gt, [8, 8, 8])))
+    for i in range(4):
+        tgt_coords = O.stride_coords(gt, [strides[i]] * 3) if strides[i] > 1 else gt
+        _, hit_rows = O.kernel_map(tgt_coords, C[i], np.zeros((1, 3), np.int64))[0]
+        want = np.zeros(len(C[i]), bool)
+        want[hit_rows] = True
+        got = targets[i].cpu().numpy()
+        assert np.array_equal(got, want), f"get_target mask differs at level {i}"
+        assert want.sum() == len(tgt_coords), "every target voxel must be reachable (training keeps targets)"
+        if i < 3:
+            keep = (Fv[i] > 0) | (want if training else False)
+            children = O.generative_coords(C[i][keep], k2 * strides[i + 1])
+            assert np.array_equal(O.canonical_coords(children), O.canonical_coords(C[i + 1])), \
+                f"generative-transpose coordinates differ at level {i + 1}"
+            assert len(C[i + 1]) == 8 * keep.sum()
+    assert np.array_equal(sout.C.cpu().numpy(), C[3][Fv[3] > 0]), "final pruning must preserve row order"
+
+
+# ---------------------------------------------------------------------------
+# CPU: the unchanged models on the oracle backend (front-end logic, no GPU)
+# ---------------------------------------------------------------------------
+def test_vae_runs_on_oracle_backend_cpu():
+    cfg, plm, coords = _vae_pair(32, 2, (8, 16, 32, 32, 4), 0)
+    with CPUB.installed():
+        loss = _vae_step(plm, coords, torch.float64, 1)
+        assert torch.isfinite(loss)
+        grads = [p.grad for p in plm.parameters() if p.grad is not None]
+        assert len(grads) > 60 and all(torch.isfinite(g).all() for g in grads)
+        out_cls, targets, sout = _decoder_levels(plm, coords, torch.float64, 1)
+        _check_levels(coords.numpy(), out_cls, targets, sout)
+
+
+def test_unet_and_minkunet_run_on_oracle_backend_cpu():
+    import MinkowskiEngine as ME
+    with CPUB.installed(), default_dtype(torch.float64):
+        cfg = W.diffusion_config(resolution=64, batch_size=2, unet_channel=(4, 16, 32, 48))
+        d = W.load_unet(cfg)
+        torch.manual_seed(0)
+        unet = d.UNet(cfg.unet_channel, cfg)
+        lat = torch.from_numpy(O.stride_coords(W.batched(W.g3_batch(64, 2)), [8, 8, 8]))
+        x = ME.SparseTensor(torch.randn(len(lat), 4), lat, tensor_stride=8)
+        out = unet(x, torch.tensor([10, 500]))
+        assert out.F.shape == (len(lat), 4) and torch.isfinite(out.F).all()
+        assert out.coordinate_map_key == x.coordinate_map_key or torch.equal(out.C, x.C)
+        mu = W.load_minkunet()
+        net = mu.MinkUNet34C(3, 5, D=3)
+        c = torch.from_numpy(O.sphere_surface(14, 0, 0))
+        y = net(ME.SparseTensor(torch.rand(len(c), 3), c))
+        assert y.F.shape == (len(c), 5) and torch.isfinite(y.F).all()
+
+
+# ---------------------------------------------------------------------------
+# GPU: engine vs the float64 oracle replay of the same graph
+# ---------------------------------------------------------------------------
+def _margin_ok(plm, coords, seed):
+    """The decoder prunes on `cls > 0`: pick noise for which no logit sits within 1e-4 of
+    the threshold in the oracle run, so fp32 round-off cannot flip a keep decision."""
+    out_cls, targets, _ = _decoder_levels(plm, coords, torch.float64, seed)
+    return min(float(t.F.abs().min()) for t in out_cls) > 1e-4
+
+
+@pytest.mark.gpu
+def test_vae_training_step_matches_oracle_replay():
+    cfg, plm, coords = _vae_pair(32, 2, (8, 16, 32, 32, 4), 0)
+    with CPUB.installed():
+        seed = next(s for s in range(1, 20) if _margin_ok(plm, coords, s))
+        ref = copy.deepcopy(plm)
+        loss_ref = _vae_step(ref, coords, torch.float64, seed)
+        lv_ref = _decoder_levels(ref, coords, torch.float64, seed)
+    gref = {n: p.grad for n, p in ref.named_parameters() if p.grad is not None}
+    names = ["model.encoder.block1.layer1.0.net.0.kernel", "model.encoder.mean_conv.kernel",
+             "model.decoder.block2.layer1.0.net.0.kernel", "model.decoder.block4.layer1.1.conv2.kernel",
+             "model.decoder.block3_cls.kernel", "model.encoder.block3.layer1.1.norm1.bn.weight"]
+    assert all(n in gref for n in names)
+    for dtype, tol_loss, tol_grad in ((torch.float64, 1e-10, 1e-8), (torch.float32, 1e-5, 2e-3)):
+        dev = copy.deepcopy(plm).to(dtype).cuda()
+        loss = _vae_step(dev, coords.cuda(), dtype, seed)
+        assert abs(float(loss) - float(loss_ref)) <= tol_loss * abs(float(loss_ref)), (dtype, float(loss), float(loss_ref))
+        gdev = {n: p.grad for n, p in dev.named_parameters() if p.grad is not None}
+        assert set(gdev) == set(gref)
+        worst = max(rel(gdev[n], gref[n]) for n in gref)
+        assert worst <= tol_grad, (dtype, worst)
+        for n in names:
+            assert rel(gdev[n], gref[n]) <= tol_grad, (dtype, n)
+        # same coordinates, masks and logits at every decoder level
+        lv = _decoder_levels(dev, coords.cuda(), dtype, seed)
+        for a, b in zip(lv[0], lv_ref[0]):
+            assert np.array_equal(O.canonical_coords(a.C.cpu().numpy()), O.canonical_coords(b.C.numpy()))
+            perm = O.row_permutation(a.C.cpu().numpy(), b.C.numpy())
+            assert rel(a.F[torch.from_numpy(perm).cuda()], b.F) <= (1e-9 if dtype == torch.float64 else 1e-3)
+        assert np.array_equal(O.canonical_coords(lv[2].C.cpu().numpy()), O.canonical_coords(lv_ref[2].C.numpy()))
+
+
+@pytest.mark.gpu
+def test_vae_decoder_levels_bit_exact_at_config2_size():
+    """BASELINE config 2: batch 16 @ 128^3, vae_channel (32,128,512,512,4)."""
+    cfg, plm, coords = _vae_pair(128, 16, (32, 128, 512, 512, 4), 0)
+    assert 600_000 < len(coords) < 900_000
+    dev = plm.float().cuda()
+    out_cls, targets, sout = _decoder_levels(dev, coords.cuda(), torch.float32, 3)
+    _check_levels(coords.numpy(), out_cls, targets, sout)
+
+
+@pytest.mark.gpu
+def test_unet_and_minkunet_match_oracle_replay():
+    import MinkowskiEngine as ME
+    with default_dtype(torch.float64):
+        cfg = W.diffusion_config(resolution=64, batch_size=2, unet_channel=(4, 16, 32, 48))
+        d = W.load_unet(cfg)
+        torch.manual_seed(0)
+        unet = d.UNet(cfg.unet_channel, cfg)
+        mu = W.load_minkunet()
+        net = mu.MinkUNet34C(3, 5, D=3)
+        lat = torch.from_numpy(O.stride_coords(W.batched(W.g3_batch(64, 2)), [8, 8, 8]))
+        xf = torch.randn(len(lat), 4)
+        c = torch.from_numpy(O.sphere_surface(14, 0, 0))
+        cf = torch.rand(len(c), 3)
+        t = torch.tensor([10, 500])
+
+    def run(model_u, model_m, device, dtype):
+        with default_dtype(dtype):
+            model_u.zero_grad(set_to_none=True)
+            model_m.zero_grad(set_to_none=True)
+            x = ME.SparseTensor(xf.to(device=device, dtype=dtype), lat.to(device), tensor_stride=8)
+            out = model_u(x, t.to(device))
+            out.F.square().mean().backward()
+            y = model_m(ME.SparseTensor(cf.to(device=device, dtype=dtype), c.to(device)))
+            y.F.square().mean().backward()
+            return out, y
+
+    with CPUB.installed():
+        ou_ref, ym_ref = run(unet, net, "cpu", torch.float64)
+    gu_ref = {n: p.grad.clone() for n, p in unet.named_parameters() if p.grad is not None}
+    gm_ref = {n: p.grad.clone() for n, p in net.named_parameters() if p.grad is not None}
+    for dtype, tol, tol_g in ((torch.float64, 1e-9, 1e-7), (torch.float32, 2e-4, 5e-3)):
+        du, dm = copy.deepcopy(unet).to(dtype).cuda(), copy.deepcopy(net).to(dtype).cuda()
+        ou, ym = run(du, dm, "cuda", dtype)
+        assert torch.equal(ou.C.cpu(), ou_ref.C) and torch.equal(ym.C.cpu(), ym_ref.C)
+        assert rel(ou.F, ou_ref.F) <= tol, (dtype, rel(ou.F, ou_ref.F))
+        assert rel(ym.F, ym_ref.F) <= tol, (dtype, rel(ym.F, ym_ref.F))
+        gu = {n: p.grad for n, p in du.named_parameters() if p.grad is not None}
+        gm = {n: p.grad for n, p in dm.named_parameters() if p.grad is not None}
+        assert set(gu) == set(gu_ref) and set(gm) == set(gm_ref)
+        assert max(rel(gu[n], gu_ref[n]) for n in gu_ref if gu_ref[n].abs().max() > 0) <= tol_g
+        assert max(rel(gm[n], gm_ref[n]) for n in gm_ref if gm_ref[n].abs().max() > 0) <= tol_g
