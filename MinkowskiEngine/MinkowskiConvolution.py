@@ -115,8 +115,6 @@ class MinkowskiConvolutionTransposeFunction(_ConvFunctionBase):
 
 
 class MinkowskiConvolutionBase(MinkowskiModuleBase):
-    __slots__ = ("in_channels", "out_channels", "is_transpose", "kernel_generator", "dimension", "use_mm",
-                 "kernel", "bias", "conv")
 
     def __init__(self, in_channels, out_channels, kernel_size=-1, stride=1, dilation=1, bias=False,
                  kernel_generator=None, is_transpose=False, is_interpolation=False, expand_coordinates=False,

@@ -83,7 +83,6 @@ class MinkowskiLocalPoolingTransposeFunction(_LocalPoolFn):
 
 
 class MinkowskiPoolingBase(MinkowskiModuleBase):
-    __slots__ = ("is_transpose", "kernel_generator", "pooling_mode", "dimension", "pooling")
 
     def __init__(self, kernel_size, stride=1, dilation=1, kernel_generator=None, is_transpose=False,
                  pooling_mode=PoolingMode.LOCAL_AVG_POOLING, dimension=-1):

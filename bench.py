@@ -463,6 +463,9 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
     n_vox = int(coords_h.shape[0])
     out = {}
     for mode in args.vae_dtypes.split(","):
+        # fp32: the engine's default fp32 policy (tensor cores where 1e-5 holds, SIMT FFMA elsewhere);
+        # fp32_tc: every fp32 convolution on the tensor cores (bf16 split, ~1e-4 on the 512-channel layers)
+        os.environ["MK_F32_TC"] = "2" if mode == "fp32_tc" else "1"
         torch.manual_seed(0)
         model, plm, _ = W.load_vae(cfg)
         if world > 1:
@@ -524,12 +527,15 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
             split["device_idle_host_gaps"] = round(max(ms - busy, 0.0), 3)
             rec["stage_ms"] = split
         out[mode] = rec
+        os.environ["MK_F32_TC"] = "1"
         del plm, model, opt, params
         torch.cuda.empty_cache()
     return {"workload": f"examples/ae_res.py VAE training_step + Adam, batch {batch}/GPU @ {res}^3 (G3 shapes), "
                         f"vae_channel (32,128,512,512,4)", "voxels_per_gpu": n_vox, "scaling": "weak",
             "h2d_bytes_per_step": int(coords_h.numel() * 4), "steps": steps, "warmup": warmup,
-            "dtypes": {"fp32": "reference default precision", "bf16": "torch.autocast(bf16) = Lightning bf16-mixed"},
+            "dtypes": {"fp32": "reference default precision (tensor cores where the 1e-5 bound holds, SIMT FFMA elsewhere)",
+                       "fp32_tc": "fp32 tensors, every convolution on the tensor cores (bf16 x3 split, MK_F32_TC=2)",
+                       "bf16": "torch.autocast(bf16) = Lightning bf16-mixed"},
             **out}
 
 
@@ -547,7 +553,7 @@ def main():
     ap.add_argument("--vae-warmup", type=int, default=3)
     ap.add_argument("--vae-res", type=int, default=128)
     ap.add_argument("--vae-batch", type=int, default=16)
-    ap.add_argument("--vae-dtypes", default="bf16,fp32")
+    ap.add_argument("--vae-dtypes", default="bf16,fp32_tc,fp32")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

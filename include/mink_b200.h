@@ -244,6 +244,31 @@ int mk_conv_wgrad_rows(int dtype, const void *x, const void *dy,
                        const uint32_t *tile_mask, int64_t ld, int64_t n_out,
                        int64_t n_in, int K, int c_in, int c_out, void *dw,
                        void *workspace, void *stream);
+/* The same two operations with the workspace SIZE passed in (workspace_bytes, from
+ * mk_conv_workspace_bytes2, which also takes n_in).  They serve everything the entry
+ * points above serve and additionally
+ *  - MK_F32 features on the tensor cores: operands are split into bf16 pieces (x = x0 +
+ *    x1 + x2, each difference exact) and the six products above 2^-24 are accumulated in
+ *    one fp32 TMEM accumulator; channels are padded to multiples of 16 in the workspace, so
+ *    the narrow layers (Cin or Cout of 1, 3, 4) take this path too.  The reference computes
+ *    fp32 (MinkowskiConvolution.py:265,285; cuBLAS SGEMM behind extern.hpp:84-114);
+ *  - dw_f32 != 0: the weight gradient of 16-bit features is written as float32
+ *    [K, Cin, Cout] (the fp32 sum the kernel holds anyway), for fp32 parameters whose
+ *    gradients are reduced over ranks in fp32 (examples/multigpu_ddp.py:81-106).
+ * workspace_bytes < what the split path needs (or -1) falls back to the SIMT kernels. */
+int64_t mk_conv_workspace_bytes2(int dtype, int64_t n_out, int64_t n_in, int K,
+                                 int c_in, int c_out);
+int mk_conv_fwd_ex(int dtype, const void *x, const void *w, int transpose_w,
+                   int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                   int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                   int c_out, void *y, const int32_t *out_rows,
+                   void *workspace, int64_t workspace_bytes, void *stream);
+int mk_conv_wgrad_ex(int dtype, const void *x, const void *dy,
+                     const int32_t *dy_rows, const int32_t *nbr,
+                     const uint32_t *tile_mask, int64_t ld, int64_t n_out,
+                     int64_t n_in, int K, int c_in, int c_out, void *dw,
+                     int dw_f32, void *workspace, int64_t workspace_bytes,
+                     void *stream);
 /* which implementation the last mk_conv_* call on this thread used:
  * 0 = SIMT tiled kernel, 1 = tcgen05/TMEM kernel */
 int mk_conv_last_path(void);

@@ -55,6 +55,9 @@ PROTOTYPES = {
     "mk_kmap_tile_order": (_i, [_p, _i64, _i64, _i, _p, _i, _i, _p, _p, _p, _p]),
     "mk_conv_wgrad": (_i, [_i, _p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _p, _p]),
     "mk_conv_wgrad_rows": (_i, [_i, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _p, _p]),
+    "mk_conv_workspace_bytes2": (_i64, [_i, _i64, _i64, _i, _i, _i]),
+    "mk_conv_fwd_ex": (_i, [_i, _p, _p, _i, _i, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _p, _p, _i64, _p]),
+    "mk_conv_wgrad_ex": (_i, [_i, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _i, _p, _i64, _p]),
     "mk_conv_last_path": (_i, []),
     "mk_conv_force_simt": (_i, [_i]),
     "mk_pool_fwd": (_i, [_i, _i, _p, _p, _i64, _i64, _i, _i, _p, _p, _p, _p]),

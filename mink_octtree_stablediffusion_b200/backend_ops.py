@@ -96,7 +96,7 @@ def _order_table(mgr, table, n_rows, ld, K, coords):
 
 def _want_order(mgr, x, n_rows, K, c_in, c_out) -> bool:
     on, n_min, _ = _tile_order_cfg()
-    return (on and n_rows >= n_min and x.dtype in (torch.bfloat16, torch.float16)
+    return (on and n_rows >= n_min and x.dtype in (torch.bfloat16, torch.float16, torch.float32)
             and bool(mgr._lib.mk_conv_tc_eligible(_dtype_code(x), n_rows, K, c_in, c_out)))
 
 
@@ -217,9 +217,13 @@ def _check_conv(in_feat, kernel, in_key, mgr, c_in_axis=1):
     _require(in_feat.size(0) == mgr.size(in_key), "in_feat.size(0) == p_map_manager->size(in_key)")
 
 
-def _workspace(lib, dtype_code, n, K, c_in, c_out, dev):
-    nbytes = int(lib.mk_conv_workspace_bytes(dtype_code, n, K, c_in, c_out))
-    return torch.empty(nbytes, dtype=torch.uint8, device=dev)
+def _workspace(lib, dtype_code, n_out, n_in, K, c_in, c_out, dev):
+    nbytes = int(lib.mk_conv_workspace_bytes2(dtype_code, n_out, n_in, K, c_in, c_out))
+    return torch.empty(nbytes, dtype=torch.uint8, device=dev), nbytes
+
+
+def _aligned16(*tensors) -> bool:
+    return not any(t.data_ptr() & 15 for t in tensors)
 
 
 def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in, c_out, order=None):
@@ -230,37 +234,34 @@ def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in,
     if n_rows == 0:
         return y
     code = _dtype_code(x)
-    ws = _workspace(lib, code, n_rows, K, c_in, c_out, x.device)
-    _lib.check(lib.mk_conv_fwd_rows(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld,
-                                    n_rows, x.size(0), K, c_in, c_out, _ptr(y), _ptr(order), _ptr(ws), _stream()))
+    ws, nbytes = _workspace(lib, code, n_rows, x.size(0), K, c_in, c_out, x.device)
+    _lib.check(lib.mk_conv_fwd_ex(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld,
+                                  n_rows, x.size(0), K, c_in, c_out, _ptr(y), _ptr(order), _ptr(ws), nbytes, _stream()))
     return y
 
 
 def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
+    """dW [K, Cin, Cout]; float32 for 16-bit features (the kernel's own fp32 sum: fp32
+    parameters then reduce un-rounded gradients over the ranks), else the feature dtype."""
     lib = mgr._lib
-    dw = torch.empty((km.K, c_in, c_out), dtype=x.dtype, device=x.device)
+    acc32 = x.dtype in (torch.bfloat16, torch.float16)
+    dw = torch.empty((km.K, c_in, c_out), dtype=torch.float32 if acc32 else x.dtype, device=x.device)
     code = _dtype_code(x)
-    ws = _workspace(lib, code, km.n_out, km.K, c_in, c_out, x.device)
+    ws, nbytes = _workspace(lib, code, km.n_out, x.size(0), km.K, c_in, c_out, x.device)
     table, mask, order = km.nbr, None, None
-    if km.n_out > 0 and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
+    if km.n_out > 0 and x.size(0) > 0 and _aligned16(x, dy) and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
         # the ordered table pairs column s with dy row order[s]; the kernel reads dy through it
         order, table, mask = _ordered(mgr, km)
-        if (x.data_ptr() | dy.data_ptr()) & 15:
-            # views at odd offsets fall to the SIMT kernel, which wants dy in table order
-            dy_o = torch.empty_like(dy)
-            _lib.check(lib.mk_rows_gather(_ptr(dy), _ptr(order), km.n_out, dy.size(1) * dy.element_size(), _ptr(dy_o),
-                                          _stream()))
-            dy, order = dy_o, None
     if mask is None:
         mask = _fwd_mask(mgr, km)
-    _lib.check(lib.mk_conv_wgrad_rows(code, _ptr(x), _ptr(dy), _ptr(order), _ptr(table), _ptr(mask), km.ld, km.n_out,
-                                      x.size(0), km.K, c_in, c_out, _ptr(dw), _ptr(ws), _stream()))
+    _lib.check(lib.mk_conv_wgrad_ex(code, _ptr(x), _ptr(dy), _ptr(order), _ptr(table), _ptr(mask), km.ld, km.n_out,
+                                    x.size(0), km.K, c_in, c_out, _ptr(dw), int(acc32), _ptr(ws), nbytes, _stream()))
     return dw
 
 
 def _conv_forward(mgr, x, w, km: _KernelMap):
     c_in, c_out = w.size(1), w.size(2)
-    if km.n_out > 0 and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
+    if km.n_out > 0 and x.size(0) > 0 and _aligned16(x) and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
         order, table, mask = _ordered(mgr, km)
         return _conv_apply(mgr, x, w, 0, 0, table, mask, km.ld, km.n_out, km.K, c_in, c_out, order)
     return _conv_apply(mgr, x, w, 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K, c_in, c_out)
@@ -309,7 +310,8 @@ def _conv_backward(in_feat, grad_out, kernel, km, mgr):
     _require(grad_out.dtype == in_feat.dtype, "grad_out_feat.scalar_type() == in_feat.scalar_type()")
     kernel = kernel.contiguous()
     # grad_in[i] = sum_k grad_out[inv[k, i]] @ W[k]^T
-    if km.n_in > 0 and _want_order(mgr, grad_out, km.n_in, km.K, kernel.size(2), kernel.size(1)):
+    if (km.n_in > 0 and km.n_out > 0 and _aligned16(grad_out)
+            and _want_order(mgr, grad_out, km.n_in, km.K, kernel.size(2), kernel.size(1))):
         order, inv, imask, ld_in, kflip = _inv_ordered(mgr, km)
         grad_in = _conv_apply(mgr, grad_out, kernel, 1, kflip, inv, imask, ld_in, km.n_in, km.K,
                               kernel.size(2), kernel.size(1), order)

@@ -11,7 +11,7 @@ int conv_fwd_simt_dispatch(int dtype, const void *x, const void *w,
 int conv_wgrad_simt_dispatch(int dtype, const void *x, const void *dy,
                              const int32_t *nbr, int64_t ld, int64_t n_out,
                              int K, int c_in, int c_out, void *dw,
-                             void *workspace, cudaStream_t st);
+                             void *workspace, cudaStream_t st, int dw_acc);
 // conv_tc.cu
 bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
 int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
@@ -19,7 +19,7 @@ int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w,
                 int kflip, const int32_t *nbr, const uint32_t *tile_mask,
                 int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
                 int c_out, void *y, const int32_t *out_rows, void *workspace,
-                cudaStream_t st);
+                cudaStream_t st, int out_f32);
 // conv_wgrad_tc.cu
 bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
 int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
@@ -27,7 +27,18 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy,
                   const int32_t *dy_rows, const int32_t *nbr,
                   const uint32_t *tile_mask, int64_t ld, int64_t n_out,
                   int64_t n_in, int K, int c_in, int c_out, void *dw,
-                  void *workspace, cudaStream_t st);
+                  void *workspace, cudaStream_t st, int dw_f32);
+// conv_f32.cu: fp32 on the tensor cores through bf16 operand splitting
+bool conv_fwd_f32_eligible(int64_t n_out, int K, int c_in, int c_out);
+bool conv_wgrad_f32_eligible(int64_t n_out, int K, int c_in, int c_out);
+int64_t conv_fwd_f32_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out);
+int64_t conv_wgrad_f32_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out);
+int conv_fwd_f32(const float *x, const float *w, int transpose_w, int kflip, const int32_t *nbr,
+                 const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                 float *y, const int32_t *out_rows, void *workspace, cudaStream_t st);
+int conv_wgrad_f32(const float *x, const float *dy, const int32_t *dy_rows, const int32_t *nbr,
+                   const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                   float *dw, void *workspace, cudaStream_t st);
 
 static thread_local int g_last_path = 0;
 static int g_force_simt = 0;
@@ -71,11 +82,24 @@ static int check_conv_args(int64_t ld, int64_t n_out, int K, int c_in,
 
 int mk_conv_tc_eligible(int dtype, int64_t n_rows, int K, int c_in,
                         int c_out) {
-  return (!g_force_simt && n_rows > 0 &&
-          conv_fwd_tc_eligible(dtype, n_rows, K, c_in, c_out) &&
+  if (g_force_simt || n_rows <= 0) return 0;
+  if (dtype == MK_F32)
+    return (conv_fwd_f32_eligible(n_rows, K, c_in, c_out) && conv_wgrad_f32_eligible(n_rows, K, c_in, c_out)) ? 1 : 0;
+  return (conv_fwd_tc_eligible(dtype, n_rows, K, c_in, c_out) &&
           conv_wgrad_tc_eligible(dtype, n_rows, K, c_in, c_out))
              ? 1
              : 0;
+}
+
+int64_t mk_conv_workspace_bytes2(int dtype, int64_t n_out, int64_t n_in, int K, int c_in, int c_out) {
+  int64_t b = mk_conv_workspace_bytes(dtype, n_out, K, c_in, c_out);
+  if (dtype == MK_F32 && n_out > 0 && n_in > 0) {
+    if (conv_fwd_f32_eligible(n_out, K, c_in, c_out))
+      b = std::max<int64_t>(b, conv_fwd_f32_workspace(n_out, n_in, K, c_in, c_out));
+    if (conv_wgrad_f32_eligible(n_out, K, c_in, c_out))
+      b = std::max<int64_t>(b, conv_wgrad_f32_workspace(n_out, n_in, K, c_in, c_out));
+  }
+  return b;
 }
 
 int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
@@ -83,9 +107,9 @@ int mk_conv_fwd(int dtype, const void *x, const void *w, int transpose_w,
                 int64_t ld, int64_t n_out, int64_t n_in,
                 int K, int c_in, int c_out, void *y, void *workspace,
                 void *stream) {
-  return mk_conv_fwd_rows(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
-                          n_out, n_in, K, c_in, c_out, y, nullptr, workspace,
-                          stream);
+  return mk_conv_fwd_ex(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
+                        n_out, n_in, K, c_in, c_out, y, nullptr, workspace, -1,
+                        stream);
 }
 
 int mk_conv_fwd_rows(int dtype, const void *x, const void *w, int transpose_w,
@@ -93,17 +117,35 @@ int mk_conv_fwd_rows(int dtype, const void *x, const void *w, int transpose_w,
                      int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
                      int c_out, void *y, const int32_t *out_rows,
                      void *workspace, void *stream) {
+  return mk_conv_fwd_ex(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
+                        n_out, n_in, K, c_in, c_out, y, out_rows, workspace, -1,
+                        stream);
+}
+
+int mk_conv_fwd_ex(int dtype, const void *x, const void *w, int transpose_w,
+                   int kflip, const int32_t *nbr, const uint32_t *tile_mask,
+                   int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                   int c_out, void *y, const int32_t *out_rows,
+                   void *workspace, int64_t workspace_bytes, void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
   if (rc) return rc;
   MK_CHECK_ARG(n_in >= 0, "n_in must be >= 0");
   if (n_out == 0) return MK_OK;
   MK_CHECK_ARG(w && nbr && y && (x || n_in == 0), "null pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  if (!g_force_simt && workspace && n_in > 0 && tc_layout_ok(x, y, nbr, ld) &&
-      conv_fwd_tc_eligible(dtype, n_out, K, c_in, c_out)) {
+  const bool tc_ok = !g_force_simt && workspace && n_in > 0 && tc_layout_ok(x, y, nbr, ld);
+  if (tc_ok && dtype != MK_F32 && conv_fwd_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
     return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
-                       n_out, n_in, K, c_in, c_out, y, out_rows, workspace, st);
+                       n_out, n_in, K, c_in, c_out, y, out_rows, workspace, st, 0);
+  }
+  // fp32: bf16 operand splitting on the tensor cores.  Needs the workspace size (it depends
+  // on n_in), so only the _ex entry point can take it.
+  if (tc_ok && dtype == MK_F32 && ((uintptr_t)w & 3) == 0 && conv_fwd_f32_eligible(n_out, K, c_in, c_out) &&
+      workspace_bytes >= conv_fwd_f32_workspace(n_out, n_in, K, c_in, c_out)) {
+    g_last_path = 1;
+    return conv_fwd_f32((const float *)x, (const float *)w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K,
+                        c_in, c_out, (float *)y, out_rows, workspace, st);
   }
   if (out_rows) {
     set_error("mk_conv_fwd_rows: an output-row permutation is only served by "
@@ -115,35 +157,52 @@ int mk_conv_fwd_rows(int dtype, const void *x, const void *w, int transpose_w,
                                 n_out, K, c_in, c_out, y, st);
 }
 
-int mk_conv_wgrad_rows(int dtype, const void *x, const void *dy,
-                       const int32_t *dy_rows, const int32_t *nbr,
-                       const uint32_t *tile_mask, int64_t ld, int64_t n_out,
-                       int64_t n_in, int K, int c_in, int c_out, void *dw,
-                       void *workspace, void *stream) {
+int mk_conv_wgrad_ex(int dtype, const void *x, const void *dy,
+                     const int32_t *dy_rows, const int32_t *nbr,
+                     const uint32_t *tile_mask, int64_t ld, int64_t n_out,
+                     int64_t n_in, int K, int c_in, int c_out, void *dw,
+                     int dw_f32, void *workspace, int64_t workspace_bytes,
+                     void *stream) {
   int rc = check_conv_args(ld, n_out, K, c_in, c_out);
   if (rc) return rc;
   MK_CHECK_ARG(n_in >= 0, "n_in must be >= 0");
   MK_CHECK_ARG(dw, "null pointer");
   MK_CHECK_ARG(n_out == 0 || (x && dy && nbr), "null pointer");
-  MK_CHECK_ARG(workspace || dtype == MK_F32 || dtype == MK_F64,
+  MK_CHECK_ARG(workspace || dtype == MK_F32 || dtype == MK_F64 || dw_f32,
                "workspace required for 16-bit dtypes");
+  MK_CHECK_ARG(!dw_f32 || dtype != MK_F64, "dw_f32 is for 16-bit and fp32 features");
+  if (dtype == MK_F32) dw_f32 = 0;   // already fp32
   cudaStream_t st = (cudaStream_t)stream;
-  if (!g_force_simt && workspace && n_in > 0 && n_out > 0 &&
-      tc_layout_ok(x, dy, nbr, ld) &&
-      (dy_rows == nullptr || ((uintptr_t)dy_rows & 15) == 0) &&
-      conv_wgrad_tc_eligible(dtype, n_out, K, c_in, c_out)) {
+  const bool tc_ok = !g_force_simt && workspace && n_in > 0 && n_out > 0 && tc_layout_ok(x, dy, nbr, ld) &&
+                     (dy_rows == nullptr || ((uintptr_t)dy_rows & 15) == 0);
+  if (tc_ok && dtype != MK_F32 && conv_wgrad_tc_eligible(dtype, n_out, K, c_in, c_out)) {
     g_last_path = 1;
     return conv_wgrad_tc(dtype, x, dy, dy_rows, nbr, tile_mask, ld, n_out,
-                         n_in, K, c_in, c_out, dw, workspace, st);
+                         n_in, K, c_in, c_out, dw, workspace, st, dw_f32);
+  }
+  if (tc_ok && dtype == MK_F32 && conv_wgrad_f32_eligible(n_out, K, c_in, c_out) &&
+      workspace_bytes >= conv_wgrad_f32_workspace(n_out, n_in, K, c_in, c_out)) {
+    g_last_path = 1;
+    return conv_wgrad_f32((const float *)x, (const float *)dy, dy_rows, nbr, tile_mask, ld, n_out, n_in, K, c_in,
+                          c_out, (float *)dw, workspace, st);
   }
   if (dy_rows) {
     set_error("mk_conv_wgrad_rows: dy_rows is served by the tensor-core path "
-              "only (16-bit dtype, eligible shape, 16-byte aligned pointers)");
+              "only (eligible shape, 16-byte aligned pointers)");
     return MK_EUNSUPPORTED;
   }
   g_last_path = 0;
   return conv_wgrad_simt_dispatch(dtype, x, dy, nbr, ld, n_out, K, c_in,
-                                  c_out, dw, workspace, st);
+                                  c_out, dw, workspace, st, dw_f32);
+}
+
+int mk_conv_wgrad_rows(int dtype, const void *x, const void *dy,
+                       const int32_t *dy_rows, const int32_t *nbr,
+                       const uint32_t *tile_mask, int64_t ld, int64_t n_out,
+                       int64_t n_in, int K, int c_in, int c_out, void *dw,
+                       void *workspace, void *stream) {
+  return mk_conv_wgrad_ex(dtype, x, dy, dy_rows, nbr, tile_mask, ld, n_out,
+                          n_in, K, c_in, c_out, dw, 0, workspace, -1, stream);
 }
 
 int mk_conv_wgrad(int dtype, const void *x, const void *dy,
@@ -151,8 +210,8 @@ int mk_conv_wgrad(int dtype, const void *x, const void *dy,
                   int64_t n_out, int64_t n_in, int K,
                   int c_in, int c_out, void *dw, void *workspace,
                   void *stream) {
-  return mk_conv_wgrad_rows(dtype, x, dy, nullptr, nbr, tile_mask, ld, n_out,
-                            n_in, K, c_in, c_out, dw, workspace, stream);
+  return mk_conv_wgrad_ex(dtype, x, dy, nullptr, nbr, tile_mask, ld, n_out,
+                          n_in, K, c_in, c_out, dw, 0, workspace, -1, stream);
 }
 
 }  // extern "C"

@@ -209,10 +209,12 @@ int conv_fwd_simt(const void *x, const void *w, int transpose_w, int kflip,
 template <typename T>
 int conv_wgrad_simt(const void *x, const void *dy, const int32_t *nbr,
                     int64_t ld, int64_t n_out, int K, int c_in, int c_out,
-                    void *dw, void *workspace, cudaStream_t st) {
+                    void *dw, void *workspace, cudaStream_t st, int dw_acc) {
   using A = typename Acc<T>::type;
   const size_t n_w = (size_t)K * c_in * c_out;
-  A *acc = std::is_same<T, A>::value ? (A *)dw : (A *)workspace;
+  // dw_acc: dw is of the accumulator type (fp32 for 16-bit features): no conversion pass
+  const bool direct = std::is_same<T, A>::value || dw_acc;
+  A *acc = direct ? (A *)dw : (A *)workspace;
   MK_CUDA(cudaMemsetAsync(acc, 0, n_w * sizeof(A), st));
   if (n_out > 0) {
     const int tiles_m = (int)ceil_div(c_in, BM), tiles_n = (int)ceil_div(c_out, BN);
@@ -228,7 +230,7 @@ int conv_wgrad_simt(const void *x, const void *dy, const int32_t *nbr,
         rows_per_split, tiles_n, acc);
     MK_LAUNCH_CHECK();
   }
-  if (!std::is_same<T, A>::value) {
+  if (!direct) {
     k_convert<T, A><<<(unsigned)ceil_div((int64_t)n_w, 256), 256, 0, st>>>(
         acc, (T *)dw, (int64_t)n_w);
     MK_LAUNCH_CHECK();
@@ -249,10 +251,10 @@ int conv_fwd_simt_dispatch(int dtype, const void *x, const void *w,
 int conv_wgrad_simt_dispatch(int dtype, const void *x, const void *dy,
                              const int32_t *nbr, int64_t ld, int64_t n_out,
                              int K, int c_in, int c_out, void *dw,
-                             void *workspace, cudaStream_t st) {
+                             void *workspace, cudaStream_t st, int dw_acc) {
   MK_DISPATCH_DTYPE(dtype, return conv_wgrad_simt<T>(x, dy, nbr, ld, n_out, K,
                                                      c_in, c_out, dw,
-                                                     workspace, st));
+                                                     workspace, st, dw_acc));
   return MK_OK;
 }
 

@@ -235,7 +235,33 @@ struct GroupQueue {
 //   bit 8 TMEM half, bits 16-18 K steps
 constexpr uint32_t kTkGroupBegin = 1u << 12, kTkGroupEnd = 1u << 13, kTkEmptyParity = 1u << 14, kTkEnd = 1u << 15;
 
-template <typename T, bool kFull>
+// 16 accumulator columns -> 16 outputs of type TOut (T: 2 x 16-byte stores; float: 4)
+template <typename T, typename TOut>
+__device__ __forceinline__ void store16(TOut *dst, const uint32_t (&v)[16]) {
+  if constexpr (sizeof(TOut) == 4) {
+    uint4 *d = reinterpret_cast<uint4 *>(dst);
+    d[0] = make_uint4(v[0], v[1], v[2], v[3]);
+    d[1] = make_uint4(v[4], v[5], v[6], v[7]);
+    d[2] = make_uint4(v[8], v[9], v[10], v[11]);
+    d[3] = make_uint4(v[12], v[13], v[14], v[15]);
+  } else {
+    uint4 o0, o1;
+    o0.x = pack2<T>(__uint_as_float(v[0]), __uint_as_float(v[1]));
+    o0.y = pack2<T>(__uint_as_float(v[2]), __uint_as_float(v[3]));
+    o0.z = pack2<T>(__uint_as_float(v[4]), __uint_as_float(v[5]));
+    o0.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
+    o1.x = pack2<T>(__uint_as_float(v[8]), __uint_as_float(v[9]));
+    o1.y = pack2<T>(__uint_as_float(v[10]), __uint_as_float(v[11]));
+    o1.z = pack2<T>(__uint_as_float(v[12]), __uint_as_float(v[13]));
+    o1.w = pack2<T>(__uint_as_float(v[14]), __uint_as_float(v[15]));
+    reinterpret_cast<uint4 *>(dst)[0] = o0;
+    reinterpret_cast<uint4 *>(dst)[1] = o1;
+  }
+}
+
+// TOut = T (16-bit features in, 16-bit out) or float (the fp32 split path of conv_f32.cu:
+// bf16 operand pieces in, the fp32 accumulator out as it is)
+template <typename T, bool kFull, typename TOut>
 __global__ void __launch_bounds__(kNumThreadsTC, 1)
 k_conv_tc(const __grid_constant__ ConvTCParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -313,7 +339,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         for (int wi = 0; wi < p.W; ++wi) touched |= __ldg(p.mask + tile * p.W + wi);
         const int64_t row = tile * kTileM + warp * 32 + lane;   // table column
         const int64_t orow = (p.out_rows && row < p.n_out) ? (int64_t)__ldg(p.out_rows + row) : row;
-        T *yrow = (T *)p.y + (size_t)orow * p.c_out + (size_t)sp * p.NT;
+        TOut *yrow = (TOut *)p.y + (size_t)orow * p.c_out + (size_t)sp * p.NT;
         const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * 256 + t * acc_stride);
         for (int c0 = 0; c0 < p.NT; c0 += 16) {
           uint32_t v[16];
@@ -324,19 +350,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) v[j] = 0u;
           }
-          if (row < p.n_out) {
-            uint4 o0, o1;
-            o0.x = pack2<T>(__uint_as_float(v[0]), __uint_as_float(v[1]));
-            o0.y = pack2<T>(__uint_as_float(v[2]), __uint_as_float(v[3]));
-            o0.z = pack2<T>(__uint_as_float(v[4]), __uint_as_float(v[5]));
-            o0.w = pack2<T>(__uint_as_float(v[6]), __uint_as_float(v[7]));
-            o1.x = pack2<T>(__uint_as_float(v[8]), __uint_as_float(v[9]));
-            o1.y = pack2<T>(__uint_as_float(v[10]), __uint_as_float(v[11]));
-            o1.z = pack2<T>(__uint_as_float(v[12]), __uint_as_float(v[13]));
-            o1.w = pack2<T>(__uint_as_float(v[14]), __uint_as_float(v[15]));
-            *reinterpret_cast<uint4 *>(yrow + c0) = o0;
-            *reinterpret_cast<uint4 *>(yrow + c0 + 8) = o1;
-          }
+          if (row < p.n_out) store16<T, TOut>(yrow + c0, v);
         }
       }
       PROF_ADD(pe_work, pe_t1);
@@ -661,11 +675,15 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
 // host side
 // ---------------------------------------------------------------------------
 static int arm_hang_report() {
-  static bool done = false;
-  if (!done) {
+  // per device: the symbol lives in each device's copy of the module
+  static bool done[64] = {};
+  int dev = 0;
+  MK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!done[dev]) {
     unsigned int *d = hang_report_device_ptr();
     MK_CUDA(cudaMemcpyToSymbol(sm100::mk_hang_slot, &d, sizeof(d)));
-    done = true;
+    done[dev] = true;
   }
   return MK_OK;
 }
@@ -744,7 +762,7 @@ int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint
   return MK_OK;
 }
 
-template <typename T>
+template <typename T, typename TOut>
 static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const void *w, int transpose_w, int kflip,
                              const int32_t *nbr, const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in,
                              int K, int c_in, int c_out, void *y, const int32_t *out_rows, void *workspace,
@@ -777,37 +795,42 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
   { int rc = arm_hang_report(); if (rc) return rc; }
   const bool full = (c_in % 64) == 0;
-  static bool attr_set[2][2] = {{false, false}, {false, false}};
-  if (!attr_set[fmt][full]) {
-    if (full)
-      MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    else
-      MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set[fmt][full] = true;
-  }
+  // (set on every call: the attribute is per device and the call costs about a microsecond)
+  if (full)
+    MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, true, TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  else
+    MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, false, TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int gx = (int)std::min<int64_t>((int64_t)p.ngroups, std::max(1, num_sms() / pl.nsplit));
   dim3 grid(gx, pl.nsplit);
   if (full)
-    k_conv_tc<T, true><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+    k_conv_tc<T, true, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
   else
-    k_conv_tc<T, false><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+    k_conv_tc<T, false, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
   MK_LAUNCH_CHECK();
   return MK_OK;
 }
 
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
                 const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
-                void *y, const int32_t *out_rows, void *workspace, cudaStream_t st) {
+                void *y, const int32_t *out_rows, void *workspace, cudaStream_t st, int out_f32) {
   TCPlan pl;
   if (!make_plan(dtype, n_out, K, c_in, c_out, pl)) {
     set_error("conv_fwd_tc: shape not eligible");
     return MK_EUNSUPPORTED;
   }
-  if (dtype == MK_BF16)
-    return conv_fwd_tc_typed<__nv_bfloat16>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K,
-                                            c_in, c_out, y, out_rows, workspace, st);
-  return conv_fwd_tc_typed<__half>(pl, 0, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, c_in, c_out,
-                                   y, out_rows, workspace, st);
+  if (dtype == MK_BF16) {
+    if (out_f32)
+      return conv_fwd_tc_typed<__nv_bfloat16, float>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in,
+                                                     K, c_in, c_out, y, out_rows, workspace, st);
+    return conv_fwd_tc_typed<__nv_bfloat16, __nv_bfloat16>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out,
+                                                           n_in, K, c_in, c_out, y, out_rows, workspace, st);
+  }
+  if (out_f32) {
+    set_error("conv_fwd_tc: fp32 output is served for bf16 operands only");
+    return MK_EUNSUPPORTED;
+  }
+  return conv_fwd_tc_typed<__half, __half>(pl, 0, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, c_in,
+                                           c_out, y, out_rows, workspace, st);
 }
 
 // weight gradient on tensor cores: conv_wgrad_tc.cu

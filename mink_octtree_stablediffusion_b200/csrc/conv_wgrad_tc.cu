@@ -522,11 +522,14 @@ k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t n, T *__restric
 // host side
 // ---------------------------------------------------------------------------
 static int arm_hang_report() {
-  static bool done = false;
-  if (!done) {
+  static bool done[64] = {};
+  int dev = 0;
+  MK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!done[dev]) {
     unsigned int *d = hang_report_device_ptr();
     MK_CUDA(cudaMemcpyToSymbol(sm100::mk_hang_slot, &d, sizeof(d)));
-    done = true;
+    done[dev] = true;
   }
   return MK_OK;
 }
@@ -588,6 +591,13 @@ bool conv_wgrad_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out
   return make_wplan(dtype, n_out, K, c_in, c_out, pl);
 }
 
+// rows of the table one CTA reduces over (its share of the tile splits)
+int64_t conv_wgrad_tc_rows_per_cta(int64_t n_out, int K, int c_in, int c_out) {
+  WPlan pl;
+  if (!make_wplan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return n_out;
+  return ((int64_t)(pl.ntiles + pl.X - 1) / pl.X) * wg::kTileM;
+}
+
 int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
   WPlan pl;
   if (!make_wplan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return 0;
@@ -596,7 +606,7 @@ int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
 
 int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_rows, const int32_t *nbr,
                   const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
-                  void *dw, void *workspace, cudaStream_t st) {
+                  void *dw, void *workspace, cudaStream_t st, int dw_f32) {
   using namespace wg;
   WPlan pl;
   if (!make_wplan(dtype, n_out, K, c_in, c_out, pl)) {
@@ -629,17 +639,15 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_ro
   p.idesc = idesc_f16(dtype == MK_BF16 ? 1 : 0, kTileM, pl.NB, 1, 1);
   p.knock = getenv("MK_WG_KNOCK") ? atoi(getenv("MK_WG_KNOCK")) : 0;
   { int rc = arm_hang_report(); if (rc) return rc; }
-  static bool attr_set = false;
-  if (!attr_set) {
-    MK_CUDA(cudaFuncSetAttribute(k_conv_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  MK_CUDA(cudaFuncSetAttribute(k_conv_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   dim3 grid(pl.X, pl.G * pl.nsplit);
   k_conv_wgrad_tc<<<grid, kThreads, pl.smem, st>>>(p, tmap_dy, tmap_dy_row);
   MK_LAUNCH_CHECK();
   const int64_t n_w = (int64_t)K * c_in * c_out;
   const unsigned blocks = (unsigned)ceil_div(n_w / 4, 32);
-  if (dtype == MK_BF16)
+  if (dw_f32)   // the fp32 sum as it is (fp32 parameters; the fp32 split path folds its blocks from it)
+    k_wgrad_reduce<float><<<blocks, 256, 0, st>>>(partial, pl.X, n_w, (float *)dw);
+  else if (dtype == MK_BF16)
     k_wgrad_reduce<__nv_bfloat16><<<blocks, 256, 0, st>>>(partial, pl.X, n_w, (__nv_bfloat16 *)dw);
   else
     k_wgrad_reduce<__half><<<blocks, 256, 0, st>>>(partial, pl.X, n_w, (__half *)dw);

@@ -86,17 +86,27 @@ def kmap_invert(nbr, n_out, ld, K, n_in):
     return inv, ld_in
 
 
-def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None, mask=None):
+def _ws(dtype, n_out, n_in, K, c_in, c_out):
+    lib = _lib.load()
+    nbytes = int(lib.mk_conv_workspace_bytes2(DT[dtype], n_out, n_in, K, c_in, c_out))
+    return torch.empty(nbytes, dtype=torch.uint8, device="cuda"), nbytes
+
+
+def conv_fwd(x, w, nbr, ld, n_out, transpose_w=0, kflip=0, c_out=None, mask=None, legacy=False):
+    """mk_conv_fwd_ex (legacy=True: the size-less mk_conv_fwd, which never takes the fp32 split path)."""
     lib = _lib.load()
     K = w.shape[0]
     c_in = x.shape[1]
     if c_out is None:
         c_out = w.shape[1] if transpose_w else w.shape[2]
     y = torch.empty((n_out, c_out), dtype=x.dtype, device="cuda")
-    ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
-                     device="cuda")
-    _lib.check(lib.mk_conv_fwd(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0], K, c_in,
-                               c_out, P(y), P(ws), S()))
+    ws, nbytes = _ws(x.dtype, n_out, x.shape[0], K, c_in, c_out)
+    if legacy:
+        _lib.check(lib.mk_conv_fwd(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0], K,
+                                   c_in, c_out, P(y), P(ws), S()))
+    else:
+        _lib.check(lib.mk_conv_fwd_ex(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0],
+                                      K, c_in, c_out, P(y), None, P(ws), nbytes, S()))
     return y
 
 
@@ -121,10 +131,9 @@ def conv_fwd_rows(x, w, nbr, ld, n_out, out_rows, transpose_w=0, kflip=0, mask=N
     c_in = x.shape[1]
     c_out = w.shape[1] if transpose_w else w.shape[2]
     y = torch.empty((n_out, c_out), dtype=x.dtype, device="cuda")
-    ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
-                     device="cuda")
-    _lib.check(lib.mk_conv_fwd_rows(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0],
-                                    K, c_in, c_out, P(y), P(out_rows), P(ws), S()))
+    ws, nbytes = _ws(x.dtype, n_out, x.shape[0], K, c_in, c_out)
+    _lib.check(lib.mk_conv_fwd_ex(DT[x.dtype], P(x), P(w), transpose_w, kflip, P(nbr), P(mask), ld, n_out, x.shape[0],
+                                  K, c_in, c_out, P(y), P(out_rows), P(ws), nbytes, S()))
     return y
 
 
@@ -135,18 +144,13 @@ def rows_gather(src, idx):
     return dst
 
 
-def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None, dy_rows=None):
+def conv_wgrad(x, dy, nbr, ld, n_out, K, mask=None, dy_rows=None, dw_f32=False):
     lib = _lib.load()
     c_in, c_out = x.shape[1], dy.shape[1]
-    dw = torch.empty((K, c_in, c_out), dtype=x.dtype, device="cuda")
-    ws = torch.empty(int(lib.mk_conv_workspace_bytes(DT[x.dtype], n_out, K, c_in, c_out)), dtype=torch.uint8,
-                     device="cuda")
-    if dy_rows is None:
-        _lib.check(lib.mk_conv_wgrad(DT[x.dtype], P(x), P(dy), P(nbr), P(mask), ld, n_out, x.shape[0], K, c_in, c_out,
-                                     P(dw), P(ws), S()))
-    else:
-        _lib.check(lib.mk_conv_wgrad_rows(DT[x.dtype], P(x), P(dy), P(dy_rows), P(nbr), P(mask), ld, n_out, x.shape[0],
-                                          K, c_in, c_out, P(dw), P(ws), S()))
+    dw = torch.empty((K, c_in, c_out), dtype=torch.float32 if dw_f32 else x.dtype, device="cuda")
+    ws, nbytes = _ws(x.dtype, n_out, x.shape[0], K, c_in, c_out)
+    _lib.check(lib.mk_conv_wgrad_ex(DT[x.dtype], P(x), P(dy), P(dy_rows), P(nbr), P(mask), ld, n_out, x.shape[0], K,
+                                    c_in, c_out, P(dw), int(dw_f32), P(ws), nbytes, S()))
     return dw
 
 

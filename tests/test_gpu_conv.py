@@ -46,6 +46,14 @@ def test_conv_fwd_bwd_same_map(dtype, cin, cout):
     tol = TOL[dtype]
     y = abi.conv_fwd(xd, wd, nbr, ld, n)
     assert rel_err(y.double().cpu().numpy(), y_ref) <= tol
+    # fp32 runs on the tensor cores too where the accumulation chain is short enough for 1e-5
+    # (bf16 operand splitting, channels padded to 16: conv_f32.cu); wide layers stay on the SIMT FFMA kernel
+    if abi.tc_eligible(dtype, n, 27, cin, cout):
+        assert abi.last_path() == 1
+    assert abi.tc_eligible(torch.float32, n, 27, cin, cout) == (cin <= 32)
+    if dtype == torch.float32:
+        y_simt = abi.conv_fwd(xd, wd, nbr, ld, n, legacy=True)      # the SIMT kernel still serves the old entry point
+        assert abi.last_path() == 0 and rel_err(y_simt.double().cpu().numpy(), y_ref) <= tol
     # data gradient: symmetric same-map shortcut (table itself, offsets mirrored) ...
     gi = abi.conv_fwd(dyd, wd, nbr, ld, n, transpose_w=1, kflip=1)
     assert rel_err(gi.double().cpu().numpy(), gi_ref) <= tol
@@ -55,6 +63,11 @@ def test_conv_fwd_bwd_same_map(dtype, cin, cout):
     assert rel_err(gi2.double().cpu().numpy(), gi_ref) <= tol
     gw = abi.conv_wgrad(xd, dyd, nbr, ld, n, 27)
     assert rel_err(gw.double().cpu().numpy(), gw_ref) <= tol
+    if dtype in (torch.bfloat16, torch.float16):
+        # fp32 weight gradient of 16-bit features (fp32 parameters): the un-rounded sum
+        gw32 = abi.conv_wgrad(xd, dyd, nbr, ld, n, 27, dw_f32=True)
+        assert gw32.dtype == torch.float32 and rel_err(gw32.double().cpu().numpy(), gw_ref) <= 1e-5
+        assert torch.equal(gw32.to(dtype), gw) or rel_err(gw32.to(dtype).double().cpu().numpy(), gw.double().cpu().numpy()) <= 1e-2
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
@@ -350,8 +363,19 @@ def test_tile_ordered_table(R, order, with_coords):
     w2 = abi.conv_wgrad(x, dy, nbr_t, ld, n, 27, dy_rows=perm)
     assert abi.last_path() == 1
     assert torch.equal(w1, w2)
-    # fp32 has no tensor-core path: a row permutation must be refused, not ignored
+    # fp64 has no tensor-core path: a row permutation must be refused, not ignored
     with pytest.raises(RuntimeError):
-        abi.conv_fwd_rows(x.float(), w.float(), nbr_t, ld, n, perm)
+        abi.conv_fwd_rows(x.double(), w.double(), nbr_t, ld, n, perm)
     with pytest.raises(RuntimeError):
-        abi.conv_wgrad(x.float(), dy.float(), nbr_t, ld, n, 27, dy_rows=perm)
+        abi.conv_wgrad(x.double(), dy.double(), nbr_t, ld, n, 27, dy_rows=perm)
+    # fp32: where the split tensor-core path serves the shape it honours the permutations too
+    x32, w32, dy32 = x.float()[:, :32].contiguous(), w.float()[:, :32].contiguous(), dy.float()
+    if abi.tc_eligible(torch.float32, n, 27, 32, 64):
+        f0 = abi.conv_fwd(x32, w32, nbr, ld, n)
+        f1 = abi.conv_fwd_rows(x32, w32, nbr_t, ld, n, perm)
+        assert abi.last_path() == 1
+        assert float((f0 - f1).abs().max() / f0.abs().max()) <= 1e-5
+        q0 = abi.conv_wgrad(x32, dy32, nbr, ld, n, 27)
+        q1 = abi.conv_wgrad(x32, dy32, nbr_t, ld, n, 27, dy_rows=perm)
+        assert abi.last_path() == 1
+        assert float((q0 - q1).abs().max() / q0.abs().max()) <= 1e-5
