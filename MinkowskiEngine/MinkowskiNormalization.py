@@ -25,6 +25,124 @@ def _like(x: SparseTensor, feats: torch.Tensor) -> SparseTensor:
     return SparseTensor(feats, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
 
 
+# ---------------------------------------------------------------------------
+# fused paths on the engine (CUDA features): one statistics pass + one affine pass
+# (mink_octtree_stablediffusion_b200/backend_norm.py, csrc/norm.cu).  CPU tensors keep the
+# composed form below (torch batch norm; global pooling + broadcast functions).
+# ---------------------------------------------------------------------------
+def _acc(t: torch.Tensor) -> torch.dtype:
+    return torch.float64 if t.dtype == torch.float64 else torch.float32
+
+
+def _bn_coef(eps):
+    def coef(mean, var, weight, bias):
+        inv = torch.rsqrt(var + eps)
+        a = inv if weight is None else inv * weight.to(inv.dtype)
+        c = -mean * a
+        if bias is not None:
+            c = c + bias.to(inv.dtype)
+        return a, c
+    return coef
+
+
+def _fused_batch_norm(bn: torch.nn.modules.batchnorm._BatchNorm, x: torch.Tensor, sync_group=False):
+    """Training-mode batch norm of the feature matrix (statistics over all rows; for
+    SyncBatchNorm over the rows of all ranks), running statistics updated like torch's
+    (`momentum`, unbiased running variance).  Returns None when the case is not served
+    (eval mode, no rows) and the caller uses torch's own."""
+    from mink_octtree_stablediffusion_b200.backend_norm import segment_norm
+    use_batch_stats = bn.training or not bn.track_running_stats or bn.running_mean is None
+    if not use_batch_stats or x.shape[0] == 0 or not x.is_floating_point():
+        return None
+    acc = _acc(x)
+    n = x.shape[0]
+    counts = torch.full((1,), float(n), dtype=acc, device=x.device)
+    reduce_fn = None
+    if sync_group is not False:
+        import torch.distributed as dist
+        group = sync_group
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            def reduce_fn(sums, cnt):
+                flat = sums.reshape(-1) if cnt is None else torch.cat([sums.reshape(-1), cnt.reshape(-1).to(sums.dtype)])
+                dist.all_reduce(flat, group=group)
+                if cnt is None:
+                    return flat.view_as(sums), None
+                return flat[:sums.numel()].view_as(sums), flat[sums.numel():].view_as(cnt)
+    # centre of the one-pass sums: the running mean when ranks must agree on it, else the first row
+    if reduce_fn is not None:
+        shift = (bn.running_mean.detach().to(acc).view(1, -1).contiguous() if bn.running_mean is not None
+                 else torch.zeros((1, x.shape[1]), dtype=acc, device=x.device))
+    else:
+        shift = x[:1].detach().to(acc).contiguous()
+    stats = []
+    y = segment_norm(x, None, 1, counts, _bn_coef(bn.eps), (bn.weight, bias_or_none(bn)), shift=shift,
+                     reduce_fn=reduce_fn, stats_out=stats)
+    if bn.training and bn.track_running_stats and bn.running_mean is not None:
+        mean, var, m = stats[0]
+        with torch.no_grad():
+            bn.num_batches_tracked.add_(1)
+            f = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+            unbiased = var * (m / (m - 1).clamp(min=1))
+            bn.running_mean.mul_(1 - f).add_(mean.view(-1).to(bn.running_mean.dtype), alpha=f)
+            bn.running_var.mul_(1 - f).add_(unbiased.view(-1).to(bn.running_var.dtype), alpha=f)
+    return y
+
+
+def bias_or_none(bn):
+    return bn.bias if bn.affine else None
+
+
+def _segments(x: SparseTensor):
+    """(seg [N] int32 batch row of every voxel, n_batch, counts [B], first row of every batch item),
+    cached on the manager beside the coordinate map."""
+    mgr = x.coordinate_manager._manager
+    cache = mgr.__dict__.setdefault("_norm_segments", {})
+    k = x.coordinate_map_key._tuple()
+    hit = cache.get(k)
+    if hit is None:
+        rows, nb = mgr._batch_of_row(x.coordinate_map_key)
+        r = rows.long()
+        counts = torch.bincount(r.clamp(min=0), minlength=nb).to(torch.float32)
+        first = torch.full((nb,), rows.numel(), dtype=torch.int64, device=rows.device)
+        first.scatter_reduce_(0, r.clamp(min=0), torch.arange(rows.numel(), device=rows.device), reduce="amin")
+        hit = cache[k] = (rows, nb, counts, first.clamp(max=max(rows.numel() - 1, 0)))
+    return hit
+
+
+def _fused_instance_norm(x: SparseTensor, coef_fn, params):
+    from mink_octtree_stablediffusion_b200.backend_norm import segment_norm
+    seg, nb, counts, first = _segments(x)
+    F_ = x.F
+    shift = F_.detach()[first].to(_acc(F_)).contiguous()
+    return segment_norm(F_, seg, nb, counts.to(_acc(F_)), coef_fn, params, shift=shift)
+
+
+def _fold_group(stat, group):
+    if group == 1:
+        return stat
+    c = stat.shape[-1]
+    g = stat.view(-1, c // group, group).mean(dim=-1)
+    return torch.repeat_interleave(g, group, dim=-1)
+
+
+def _stable_coef(eps, fold):
+    """Coefficients of the fork's 'stable' norms from the per-channel statistics: the data are
+    centred with the FOLDED mean mu_g, so the per-channel second moment about it is
+    var_c + (mean_c - mu_g)^2, which is then folded as well (MinkowskiNormalization.py:347-402)."""
+    def coef(mean, var, weight, bias, *ada):
+        mu = fold(mean)
+        v = fold(var + (mean - mu) ** 2)
+        inv = torch.rsqrt(v + eps)
+        a = inv * weight.to(inv.dtype)
+        c = bias.to(inv.dtype) - mu * a
+        if ada:                      # AdaIN: (y w + b) (1 + scale[batch]) + shift[batch]
+            scale, shift = ada
+            a = a * (1 + scale.to(inv.dtype))
+            c = c * (1 + scale.to(inv.dtype)) + shift.to(inv.dtype)
+        return a, c
+    return coef
+
+
 class MinkowskiBatchNorm(Module):
     """torch.nn.BatchNorm1d over the feature rows of a sparse tensor."""
 
@@ -34,7 +152,9 @@ class MinkowskiBatchNorm(Module):
                                        track_running_stats=track_running_stats)
 
     def forward(self, input):
-        return _like(input, self.bn(input.F))
+        x = input.F
+        y = _fused_batch_norm(self.bn, x) if x.is_cuda else None
+        return _like(input, self.bn(x) if y is None else y)
 
     def __repr__(self):
         bn = self.bn
@@ -51,6 +171,11 @@ class MinkowskiSyncBatchNorm(MinkowskiBatchNorm):
         Module.__init__(self)
         self.bn = torch.nn.SyncBatchNorm(num_features, eps=eps, momentum=momentum, affine=affine,
                                          track_running_stats=track_running_stats, process_group=process_group)
+
+    def forward(self, input):
+        x = input.F
+        y = _fused_batch_norm(self.bn, x, sync_group=self.bn.process_group) if x.is_cuda else None
+        return _like(input, self.bn(x) if y is None else y)
 
     @classmethod
     def convert_sync_batchnorm(cls, module, process_group=None):
@@ -114,6 +239,8 @@ class MinkowskiInstanceNorm(MinkowskiModuleBase):
 
     def forward(self, input: SparseTensor):
         assert isinstance(input, SparseTensor)
+        if input.F.is_cuda:
+            return _like(input, _fused_instance_norm(input, _stable_coef(self.eps, lambda s: s), (self.weight, self.bias)))
         y = _instance_standardise(input, self.eps)
         return _like(input, y * self.weight + self.bias)
 
@@ -156,6 +283,13 @@ class MinkowskiStableInstanceNorm(MinkowskiModuleBase):
         return torch.repeat_interleave(g, self.group, dim=-1)
 
     def forward(self, x):
+        if x.F.is_cuda:
+            g = self.group
+
+            def coef(mean, var, weight, bias):
+                return _stable_coef(self.eps, self._fold)(mean, var, torch.repeat_interleave(weight, g, dim=-1),
+                                                           torch.repeat_interleave(bias, g, dim=-1))
+            return _like(x, _fused_instance_norm(x, coef, (self.weight, self.bias)))
         y = _instance_standardise(x, self.eps, self._fold)
         scale = torch.repeat_interleave(self.weight, self.group, dim=-1)
         shift = torch.repeat_interleave(self.bias, self.group, dim=-1)
@@ -188,6 +322,8 @@ class MinkowskiStableGroupNorm(MinkowskiModuleBase):
 
     def forward(self, x):
         fold = lambda s: s.mean(dim=1, keepdim=True).repeat(1, self.num_features)  # noqa: E731
+        if x.F.is_cuda:
+            return _like(x, _fused_instance_norm(x, _stable_coef(self.eps, fold), (self.weight, self.bias)))
         y = _instance_standardise(x, self.eps, fold)
         return _like(x, y * self.weight + self.bias)
 
@@ -233,6 +369,11 @@ class AdaStableInstanceNorm(MinkowskiModuleBase):
 
     def forward(self, x, emb):
         scale, shift = self.linear(emb).chunk(2, dim=1)
+        if x.F.is_cuda and scale.shape[0] == _segments(x)[1]:
+            # scale / shift rows are indexed by batch INDEX; the segments are the rows of the origin map,
+            # which are ordered by batch index (row b == batch b when the indices are 0..B-1)
+            return _like(x, _fused_instance_norm(x, _stable_coef(self.eps, lambda s: s),
+                                                 (self.weight, self.bias, scale, shift)))
         y = _instance_standardise(x, self.eps)
         b = x.C[:, 0].long()
         return _like(x, (y * self.weight + self.bias) * (1 + scale[b]) + shift[b])

@@ -312,6 +312,29 @@ int mk_broadcast_bwd(int dtype, int mode, const void *x, const void *g,
                      int c, int64_t n_batch, void *dx, void *dg,
                      void *workspace, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Normalisation passes.  Replace, for MinkowskiBatchNorm / SyncBatchNorm
+ * (MinkowskiNormalization.py:55-195) and the instance-norm family (:198-622:
+ * two GlobalPooling + three Broadcast calls + elementwise torch ops per layer,
+ * extern.hpp:332-392), every full pass over [N, C] by one statistics read and
+ * one normalise+affine read/write.  A segment is a batch item (seg_of_row, the
+ * batch row of every voxel; negative = row ignored) or the whole tensor
+ * (seg_of_row == NULL, n_seg = 1).  Sums and coefficients are float32 (float64
+ * for MK_F64 features), shaped [n_seg, 2, c] / [n_seg, c].
+ *   mk_seg_sums:   out[s][0][c] = sum_r (a - shift_a[s,c]),
+ *                  out[s][1][c] = sum_r (a - shift_a[s,c]) * (b - shift_b[s,c])
+ *                  (shift_* may be NULL = 0; out is zeroed by the call)
+ *   mk_seg_affine: out[r,c] = coef_a[s,c] * a[r,c] + coef_b[s,c] * b[r,c] + coef_c[s,c]
+ *                  (coef_b / b may be NULL)
+ * ---------------------------------------------------------------------- */
+int mk_seg_sums(int dtype, const void *a, const void *b, const void *shift_a,
+                const void *shift_b, const int32_t *seg_of_row, int64_t n, int c,
+                int64_t n_seg, void *out, void *stream);
+int mk_seg_affine(int dtype, const void *a, const void *b,
+                  const int32_t *seg_of_row, int64_t n, int c,
+                  const void *coef_a, const void *coef_b, const void *coef_c,
+                  void *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,8 @@ PROTOTYPES = {
     "mk_global_pool_bwd": (_i, [_i, _i, _p, _p, _p, _i64, _i, _i64, _p, _p, _p]),
     "mk_broadcast_fwd": (_i, [_i, _i, _p, _p, _p, _i64, _i, _p, _p]),
     "mk_broadcast_bwd": (_i, [_i, _i, _p, _p, _p, _p, _i64, _i, _i64, _p, _p, _p, _p]),
+    "mk_seg_sums": (_i, [_i, _p, _p, _p, _p, _p, _i64, _i, _i64, _p, _p]),
+    "mk_seg_affine": (_i, [_i, _p, _p, _p, _i64, _i, _p, _p, _p, _p, _p]),
 }
 
 _lib = None

@@ -1,0 +1,121 @@
+"""Fused normalisation on the engine's two passes (csrc/norm.cu): one statistics
+read (`mk_seg_sums`) and one normalise + affine read/write (`mk_seg_affine`).
+
+`segment_norm` is the one autograd Function behind MinkowskiBatchNorm /
+MinkowskiSyncBatchNorm and the instance-norm family (reference:
+MinkowskiNormalization.py:55-195, :198-622).  The layer-specific part — how the
+per-(segment, channel) mean and variance turn into the affine coefficients
+y = A x + C (batch-norm weight/bias, the fork's group folding, AdaIN scale/shift)
+— is a small torch function on [n_seg, C] tensors and is differentiated by
+autograd itself; only the two passes over [N, C] are kernels:
+
+    forward   S = seg_sums(x - K, (x - K)^2)      mean = K + S0/m,  var = S1/m - (S0/m)^2
+              A, C = coef(mean, var, *params)     y = A[seg] x + C[seg]
+    backward  dA = sum dy x, dC = sum dy          (one seg_sums pass)
+              dmean, dvar, dparams = autograd(coef)
+              dx = A dy + (2 dvar / m) (x - mean) + dmean / m      (one affine pass)
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Callable, Optional, Sequence
+
+import torch
+
+from . import _lib
+from .backend import _dtype_code, _ptr, _stream
+
+
+def _acc_dtype(t: torch.Tensor) -> torch.dtype:
+    return torch.float64 if t.dtype == torch.float64 else torch.float32
+
+
+def seg_sums(a: torch.Tensor, b: torch.Tensor, shift_a: Optional[torch.Tensor], shift_b: Optional[torch.Tensor],
+             seg: Optional[torch.Tensor], n_seg: int) -> torch.Tensor:
+    """[n_seg, 2, C]: sum (a - shift_a), sum (a - shift_a) * (b - shift_b) per segment and channel."""
+    lib = _lib.load()
+    n, c = a.shape
+    out = torch.empty((n_seg, 2, c), dtype=_acc_dtype(a), device=a.device)
+    _lib.check(lib.mk_seg_sums(_dtype_code(a), _ptr(a), _ptr(b), _ptr(shift_a), _ptr(shift_b), _ptr(seg), n, c, n_seg,
+                               ctypes.c_void_p(out.data_ptr()), _stream()))
+    return out
+
+
+def seg_affine(a: torch.Tensor, b: Optional[torch.Tensor], seg: Optional[torch.Tensor], coef_a: torch.Tensor,
+               coef_b: Optional[torch.Tensor], coef_c: torch.Tensor) -> torch.Tensor:
+    """out[r] = coef_a[seg[r]] * a[r] + coef_b[seg[r]] * b[r] + coef_c[seg[r]]."""
+    lib = _lib.load()
+    n, c = a.shape
+    out = torch.empty_like(a)
+    _lib.check(lib.mk_seg_affine(_dtype_code(a), _ptr(a), _ptr(b), _ptr(seg), n, c, _ptr(coef_a), _ptr(coef_b),
+                                 _ptr(coef_c), _ptr(out), _stream()))
+    return out
+
+
+class _SegmentNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, seg, n_seg, counts, shift, coef_fn, reduce_fn, stats_out, *params):
+        x = x.contiguous()
+        acc = _acc_dtype(x)
+        S = seg_sums(x, x, shift, shift, seg, n_seg)
+        m = counts
+        if reduce_fn is not None:            # SyncBatchNorm: sums and counts over all ranks
+            S, m = reduce_fn(S, m)
+        m = m.to(acc).clamp(min=1).view(-1, 1)
+        d = S[:, 0] / m
+        mean = d if shift is None else shift + d
+        var = (S[:, 1] / m - d * d).clamp(min=0)
+        if stats_out is not None:
+            stats_out.append((mean.detach(), var.detach(), m))
+        mean_l, var_l = mean.detach().requires_grad_(True), var.detach().requires_grad_(True)
+        with torch.enable_grad():
+            p_l = [p.detach().requires_grad_(p.requires_grad) if isinstance(p, torch.Tensor) else p for p in params]
+            A, C = coef_fn(mean_l, var_l, *p_l)
+            A, C = A.to(acc).expand(n_seg, x.shape[1]).contiguous(), C.to(acc).expand(n_seg, x.shape[1]).contiguous()
+        y = seg_affine(x, None, seg, A.detach(), None, C.detach())
+        ctx.save_for_backward(x, seg, mean.detach(), m)
+        ctx.graph = (mean_l, var_l, p_l, A, C)
+        ctx.n_seg, ctx.reduce_fn = n_seg, reduce_fn
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, seg, mean, m = ctx.saved_tensors
+        mean_l, var_l, p_l, A, C = ctx.graph
+        dy = dy.contiguous()
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        # dC = sum dy, dA = sum dy * x  (x taken relative to the mean: no cancellation; dA is corrected below)
+        S = seg_sums(dy, x, None, mean, seg, ctx.n_seg)
+        dC = S[:, 0]
+        dA = S[:, 1] + mean * dC
+        wanted = [mean_l, var_l] + [p for p in p_l if isinstance(p, torch.Tensor) and p.requires_grad]
+        grads = torch.autograd.grad([A, C], wanted, [dA, dC], allow_unused=True)
+        dmean = grads[0] if grads[0] is not None else torch.zeros_like(mean)
+        dvar = grads[1] if grads[1] is not None else torch.zeros_like(mean)
+        if ctx.reduce_fn is not None:        # the statistics were global: so are their gradients
+            both, _ = ctx.reduce_fn(torch.stack([dmean, dvar], dim=1), None)
+            dmean, dvar = both[:, 0], both[:, 1]
+        cb = 2.0 * dvar / m
+        cc = dmean / m - cb * mean
+        dx = seg_affine(dy, x, seg, A.detach(), cb.contiguous(), cc.contiguous())
+        out, gi = [], 2
+        for p in p_l:
+            if isinstance(p, torch.Tensor) and p.requires_grad:
+                out.append(grads[gi])
+                gi += 1
+            else:
+                out.append(None)
+        return (dx, None, None, None, None, None, None, None, *out)
+
+
+def segment_norm(x: torch.Tensor, seg: Optional[torch.Tensor], n_seg: int, counts: torch.Tensor,
+                 coef_fn: Callable, params: Sequence = (), shift: Optional[torch.Tensor] = None, reduce_fn=None,
+                 stats_out: Optional[list] = None) -> torch.Tensor:
+    """y[r] = A[seg[r]] * x[r] + C[seg[r]] with (A, C) = coef_fn(mean, var, *params), where mean / var
+    ([n_seg, C], biased variance) are the statistics of x over each segment's rows.
+
+    counts [n_seg]: rows per segment; shift [n_seg, C] (optional): any value near the segment mean, used
+    to centre the one-pass sums; reduce_fn(sums, counts) -> (sums, counts) all-reduces them over ranks;
+    stats_out (optional list) receives (mean, var, count) for running-statistics updates."""
+    return _SegmentNorm.apply(x, seg, n_seg, counts, shift, coef_fn, reduce_fn, stats_out, *params)

@@ -217,6 +217,9 @@ def _check_conv(in_feat, kernel, in_key, mgr, c_in_axis=1):
     _require(in_feat.size(0) == mgr.size(in_key), "in_feat.size(0) == p_map_manager->size(in_key)")
 
 
+CONV_LOG = None      # development aid: set to a list to record (kind, n_out, n_in, K, c_in, c_out, dtype) per launch
+
+
 def _workspace(lib, dtype_code, n_out, n_in, K, c_in, c_out, dev):
     nbytes = int(lib.mk_conv_workspace_bytes2(dtype_code, n_out, n_in, K, c_in, c_out))
     return torch.empty(nbytes, dtype=torch.uint8, device=dev), nbytes
@@ -234,6 +237,8 @@ def _conv_apply(mgr, x, w, transpose_w, kflip, table, mask, ld, n_rows, K, c_in,
     if n_rows == 0:
         return y
     code = _dtype_code(x)
+    if CONV_LOG is not None:
+        CONV_LOG.append(("dgrad" if transpose_w else "fwd", n_rows, x.size(0), K, c_in, c_out, str(x.dtype), order is not None))
     ws, nbytes = _workspace(lib, code, n_rows, x.size(0), K, c_in, c_out, x.device)
     _lib.check(lib.mk_conv_fwd_ex(code, _ptr(x), _ptr(w), int(transpose_w), int(kflip), _ptr(table), _ptr(mask), ld,
                                   n_rows, x.size(0), K, c_in, c_out, _ptr(y), _ptr(order), _ptr(ws), nbytes, _stream()))
@@ -254,6 +259,8 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
         order, table, mask = _ordered(mgr, km)
     if mask is None:
         mask = _fwd_mask(mgr, km)
+    if CONV_LOG is not None:
+        CONV_LOG.append(("wgrad", km.n_out, x.size(0), km.K, c_in, c_out, str(x.dtype), order is not None))
     _lib.check(lib.mk_conv_wgrad_ex(code, _ptr(x), _ptr(dy), _ptr(order), _ptr(table), _ptr(mask), km.ld, km.n_out,
                                     x.size(0), km.K, c_in, c_out, _ptr(dw), int(acc32), _ptr(ws), nbytes, _stream()))
     return dw

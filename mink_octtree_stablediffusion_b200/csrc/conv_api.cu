@@ -40,6 +40,18 @@ int conv_wgrad_f32(const float *x, const float *dy, const int32_t *dy_rows, cons
                    const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
                    float *dw, void *workspace, cudaStream_t st);
 
+// ... and zero-padding of narrow 16-bit layers to 16 channels
+bool conv_fwd_pad16_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
+bool conv_wgrad_pad16_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
+int64_t conv_fwd_pad16_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out);
+int64_t conv_wgrad_pad16_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out);
+int conv_fwd_pad16(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
+                   const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                   void *y, const int32_t *out_rows, void *workspace, cudaStream_t st);
+int conv_wgrad_pad16(int dtype, const void *x, const void *dy, const int32_t *dy_rows, const int32_t *nbr,
+                     const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                     void *dw, int dw_f32, void *workspace, cudaStream_t st);
+
 static thread_local int g_last_path = 0;
 static int g_force_simt = 0;
 }  // namespace mk
@@ -85,6 +97,9 @@ int mk_conv_tc_eligible(int dtype, int64_t n_rows, int K, int c_in,
   if (g_force_simt || n_rows <= 0) return 0;
   if (dtype == MK_F32)
     return (conv_fwd_f32_eligible(n_rows, K, c_in, c_out) && conv_wgrad_f32_eligible(n_rows, K, c_in, c_out)) ? 1 : 0;
+  if ((c_in % 16) || (c_out % 16))
+    return (conv_fwd_pad16_eligible(dtype, n_rows, K, c_in, c_out) &&
+            conv_wgrad_pad16_eligible(dtype, n_rows, K, c_in, c_out)) ? 1 : 0;
   return (conv_fwd_tc_eligible(dtype, n_rows, K, c_in, c_out) &&
           conv_wgrad_tc_eligible(dtype, n_rows, K, c_in, c_out))
              ? 1
@@ -98,6 +113,12 @@ int64_t mk_conv_workspace_bytes2(int dtype, int64_t n_out, int64_t n_in, int K, 
       b = std::max<int64_t>(b, conv_fwd_f32_workspace(n_out, n_in, K, c_in, c_out));
     if (conv_wgrad_f32_eligible(n_out, K, c_in, c_out))
       b = std::max<int64_t>(b, conv_wgrad_f32_workspace(n_out, n_in, K, c_in, c_out));
+  }
+  if ((dtype == MK_BF16 || dtype == MK_F16) && n_out > 0 && n_in > 0) {
+    if (conv_fwd_pad16_eligible(dtype, n_out, K, c_in, c_out))
+      b = std::max<int64_t>(b, conv_fwd_pad16_workspace(n_out, n_in, K, c_in, c_out));
+    if (conv_wgrad_pad16_eligible(dtype, n_out, K, c_in, c_out))
+      b = std::max<int64_t>(b, conv_wgrad_pad16_workspace(n_out, n_in, K, c_in, c_out));
   }
   return b;
 }
@@ -139,6 +160,12 @@ int mk_conv_fwd_ex(int dtype, const void *x, const void *w, int transpose_w,
     return conv_fwd_tc(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld,
                        n_out, n_in, K, c_in, c_out, y, out_rows, workspace, st, 0);
   }
+  if (tc_ok && conv_fwd_pad16_eligible(dtype, n_out, K, c_in, c_out) &&
+      workspace_bytes >= conv_fwd_pad16_workspace(n_out, n_in, K, c_in, c_out)) {
+    g_last_path = 1;
+    return conv_fwd_pad16(dtype, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, c_in, c_out, y, out_rows,
+                          workspace, st);
+  }
   // fp32: bf16 operand splitting on the tensor cores.  Needs the workspace size (it depends
   // on n_in), so only the _ex entry point can take it.
   if (tc_ok && dtype == MK_F32 && ((uintptr_t)w & 3) == 0 && conv_fwd_f32_eligible(n_out, K, c_in, c_out) &&
@@ -179,6 +206,12 @@ int mk_conv_wgrad_ex(int dtype, const void *x, const void *dy,
     g_last_path = 1;
     return conv_wgrad_tc(dtype, x, dy, dy_rows, nbr, tile_mask, ld, n_out,
                          n_in, K, c_in, c_out, dw, workspace, st, dw_f32);
+  }
+  if (tc_ok && conv_wgrad_pad16_eligible(dtype, n_out, K, c_in, c_out) &&
+      workspace_bytes >= conv_wgrad_pad16_workspace(n_out, n_in, K, c_in, c_out)) {
+    g_last_path = 1;
+    return conv_wgrad_pad16(dtype, x, dy, dy_rows, nbr, tile_mask, ld, n_out, n_in, K, c_in, c_out, dw, dw_f32,
+                            workspace, st);
   }
   if (tc_ok && dtype == MK_F32 && conv_wgrad_f32_eligible(n_out, K, c_in, c_out) &&
       workspace_bytes >= conv_wgrad_f32_workspace(n_out, n_in, K, c_in, c_out)) {

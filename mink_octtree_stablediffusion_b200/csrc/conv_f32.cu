@@ -202,6 +202,154 @@ int64_t conv_wgrad_f32_workspace(int64_t n_out, int64_t n_in, int K, int c_in, i
                    (size_t)conv_wgrad_tc_workspace(n_out, K, t.nw * cip, t.nw * cop) + 256);
 }
 
+// ---------------------------------------------------------------------------
+// 16-bit features with channel counts that are not multiples of 16 (the 1 -> 32, 512 -> 4,
+// 4 -> 4, 4 -> 512 layers of the octree VAE, examples/ae_res.py:973; the 3 -> 32 stem of
+// MinkUNet): operands are zero-padded to 16 channels in the workspace and run on the
+// tensor-core kernels; the padded output columns are dropped.
+// ---------------------------------------------------------------------------
+namespace {
+template <typename T>
+__global__ void k_pad_rows(const T *__restrict__ x, int64_t n, int c, int cp, T *__restrict__ out) {
+  const int64_t total = n * cp;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = e / cp;
+    const int ch = (int)(e - r * cp);
+    out[e] = ch < c ? x[r * c + ch] : T(0.f);
+  }
+}
+
+// w [K, a, b] -> out [K, ap, bp] (zero padded)
+template <typename T>
+__global__ void k_pad_w(const T *__restrict__ w, int K, int a, int b, int ap, int bp, T *__restrict__ out) {
+  const int64_t total = (int64_t)K * ap * bp;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = e;
+    const int j = (int)(r % bp); r /= bp;
+    const int i = (int)(r % ap);
+    const int k = (int)(r / ap);
+    out[e] = (i < a && j < b) ? w[((size_t)k * a + i) * b + j] : T(0.f);
+  }
+}
+
+// y [.., a, b] = yp [.., ap, bp][:a, :b]   (rows = K * a for weights, n for features with a = 1 ... handled by caller)
+template <typename T>
+__global__ void k_unpad(const T *__restrict__ yp, int64_t outer, int a, int b, int ap, int bp, T *__restrict__ y) {
+  const int64_t total = outer * a * b;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = e;
+    const int j = (int)(r % b); r /= b;
+    const int i = (int)(r % a);
+    const int64_t o = r / a;
+    y[e] = yp[((size_t)o * ap + i) * bp + j];
+  }
+}
+}  // namespace
+
+bool conv_pad16_needed(int c_in, int c_out) { return (c_in % 16) != 0 || (c_out % 16) != 0; }
+
+bool conv_fwd_pad16_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) {
+  return (dtype == MK_BF16 || dtype == MK_F16) && conv_pad16_needed(c_in, c_out) &&
+         conv_fwd_tc_eligible(dtype, n_out, K, pad16(c_in), pad16(c_out));
+}
+
+bool conv_wgrad_pad16_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) {
+  return (dtype == MK_BF16 || dtype == MK_F16) && conv_pad16_needed(c_in, c_out) &&
+         conv_wgrad_tc_eligible(dtype, n_out, K, pad16(c_in), pad16(c_out));
+}
+
+int64_t conv_fwd_pad16_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out) {
+  const int cip = pad16(c_in), cop = pad16(c_out);
+  return (int64_t)((cip != c_in ? al256((size_t)n_in * cip * 2) : 0) + al256((size_t)K * cip * cop * 2) +
+                   (cop != c_out ? al256((size_t)n_out * cop * 2) : 0) +
+                   (size_t)conv_fwd_tc_workspace(n_out, K, cip, cop) + 256);
+}
+
+int64_t conv_wgrad_pad16_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out) {
+  const int cip = pad16(c_in), cop = pad16(c_out);
+  return (int64_t)((cip != c_in ? al256((size_t)n_in * cip * 2) : 0) + (cop != c_out ? al256((size_t)n_out * cop * 2) : 0) +
+                   al256((size_t)K * cip * cop * 4) + (size_t)conv_wgrad_tc_workspace(n_out, K, cip, cop) + 256);
+}
+
+template <typename T>
+static int conv_fwd_pad16_t(int dtype, const T *x, const T *w, int transpose_w, int kflip, const int32_t *nbr,
+                            const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                            int c_out, T *y, const int32_t *out_rows, void *workspace, cudaStream_t st) {
+  const int cip = pad16(c_in), cop = pad16(c_out);
+  uint8_t *ws = (uint8_t *)workspace;
+  const T *xp = x;
+  if (cip != c_in) {
+    T *buf = (T *)ws; ws += al256((size_t)n_in * cip * 2);
+    k_pad_rows<T><<<grid_for(n_in * cip, 256), 256, 0, st>>>(x, n_in, c_in, cip, buf);
+    MK_LAUNCH_CHECK();
+    xp = buf;
+  }
+  T *wp = (T *)ws; ws += al256((size_t)K * cip * cop * 2);
+  if (!transpose_w) k_pad_w<T><<<grid_for((int64_t)K * cip * cop, 256), 256, 0, st>>>(w, K, c_in, c_out, cip, cop, wp);
+  else              k_pad_w<T><<<grid_for((int64_t)K * cip * cop, 256), 256, 0, st>>>(w, K, c_out, c_in, cop, cip, wp);
+  MK_LAUNCH_CHECK();
+  T *yp = y;
+  if (cop != c_out) { yp = (T *)ws; ws += al256((size_t)n_out * cop * 2); }
+  int rc = conv_fwd_tc(dtype, xp, wp, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, cip, cop, yp, out_rows, ws,
+                       st, 0);
+  if (rc) return rc;
+  if (yp != y) {
+    k_unpad<T><<<grid_for(n_out * c_out, 256), 256, 0, st>>>(yp, n_out, 1, c_out, 1, cop, y);
+    MK_LAUNCH_CHECK();
+  }
+  return MK_OK;
+}
+
+int conv_fwd_pad16(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
+                   const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                   void *y, const int32_t *out_rows, void *workspace, cudaStream_t st) {
+  if (dtype == MK_BF16)
+    return conv_fwd_pad16_t<__nv_bfloat16>(dtype, (const __nv_bfloat16 *)x, (const __nv_bfloat16 *)w, transpose_w, kflip,
+                                           nbr, tile_mask, ld, n_out, n_in, K, c_in, c_out, (__nv_bfloat16 *)y, out_rows,
+                                           workspace, st);
+  return conv_fwd_pad16_t<__half>(dtype, (const __half *)x, (const __half *)w, transpose_w, kflip, nbr, tile_mask, ld,
+                                  n_out, n_in, K, c_in, c_out, (__half *)y, out_rows, workspace, st);
+}
+
+template <typename T>
+static int conv_wgrad_pad16_t(int dtype, const T *x, const T *dy, const int32_t *dy_rows, const int32_t *nbr,
+                              const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in,
+                              int c_out, void *dw, int dw_f32, void *workspace, cudaStream_t st) {
+  const int cip = pad16(c_in), cop = pad16(c_out);
+  uint8_t *ws = (uint8_t *)workspace;
+  const T *xp = x, *dyp = dy;
+  if (cip != c_in) {
+    T *buf = (T *)ws; ws += al256((size_t)n_in * cip * 2);
+    k_pad_rows<T><<<grid_for(n_in * cip, 256), 256, 0, st>>>(x, n_in, c_in, cip, buf);
+    MK_LAUNCH_CHECK();
+    xp = buf;
+  }
+  if (cop != c_out) {
+    T *buf = (T *)ws; ws += al256((size_t)n_out * cop * 2);
+    k_pad_rows<T><<<grid_for(n_out * cop, 256), 256, 0, st>>>(dy, n_out, c_out, cop, buf);
+    MK_LAUNCH_CHECK();
+    dyp = buf;
+  }
+  float *dwp = (float *)ws; ws += al256((size_t)K * cip * cop * 4);
+  int rc = conv_wgrad_tc(dtype, xp, dyp, dy_rows, nbr, tile_mask, ld, n_out, n_in, K, cip, cop, dwp, ws, st, dw_f32);
+  if (rc) return rc;
+  const int64_t total = (int64_t)K * c_in * c_out;
+  if (dw_f32) k_unpad<float><<<grid_for(total, 256), 256, 0, st>>>(dwp, K, c_in, c_out, cip, cop, (float *)dw);
+  else        k_unpad<T><<<grid_for(total, 256), 256, 0, st>>>((const T *)dwp, K, c_in, c_out, cip, cop, (T *)dw);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+int conv_wgrad_pad16(int dtype, const void *x, const void *dy, const int32_t *dy_rows, const int32_t *nbr,
+                     const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                     void *dw, int dw_f32, void *workspace, cudaStream_t st) {
+  if (dtype == MK_BF16)
+    return conv_wgrad_pad16_t<__nv_bfloat16>(dtype, (const __nv_bfloat16 *)x, (const __nv_bfloat16 *)dy, dy_rows, nbr,
+                                             tile_mask, ld, n_out, n_in, K, c_in, c_out, dw, dw_f32, workspace, st);
+  return conv_wgrad_pad16_t<__half>(dtype, (const __half *)x, (const __half *)dy, dy_rows, nbr, tile_mask, ld, n_out,
+                                    n_in, K, c_in, c_out, dw, dw_f32, workspace, st);
+}
+
 // y (fp32) = conv(x (fp32), w (fp32)) through the bf16 tensor-core kernel
 int conv_fwd_f32(const float *x, const float *w, int transpose_w, int kflip, const int32_t *nbr,
                  const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,

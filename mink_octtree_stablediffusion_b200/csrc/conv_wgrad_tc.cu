@@ -549,7 +549,9 @@ bool make_wplan(int dtype, int64_t n_out, int K, int c_in, int c_out, WPlan &pl)
   if (n_out > (int64_t)kTileM * 0x7fffff00) return false;
   pl.pa = (c_in + 63) / 64;
   pl.npairs = (K * pl.pa + 1) / 2;
-  int nsplit = (c_out + 255) / 256;
+  int nb_max = 128;   // 128-column accumulators: dy tile of 32 KB, four A stages in flight (256: 64 KB tile, two stages; 512 -> 512 wgrad 325 -> 508 TFLOP/s)
+  if (const char *e = getenv("MK_WG_NB")) nb_max = std::max(16, std::min(256, atoi(e)));   // development knob
+  int nsplit = (c_out + nb_max - 1) / nb_max;
   while (c_out % (16 * nsplit)) ++nsplit;
   pl.nsplit = nsplit;
   pl.NB = c_out / nsplit;

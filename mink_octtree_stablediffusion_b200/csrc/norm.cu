@@ -1,0 +1,287 @@
+// Segment statistics and per-segment affine maps: the two passes every
+// normalisation layer of the example networks is made of.
+//
+// Replaces, for MinkowskiBatchNorm / MinkowskiSyncBatchNorm (MinkowskiNormalization.py:
+// 55-195, torch.nn.BatchNorm1d on the feature matrix) and for the instance-norm family
+// (MinkowskiInstanceNorm :198-314, the fork's MinkowskiStableInstanceNorm :317-402 and
+// AdaStableInstanceNorm :546-622: two GlobalPooling + three Broadcast launches + ~10
+// elementwise torch ops per call, extern.hpp:332-392), the chain of full passes over
+// [N, C] by one read (statistics) and one read + write (normalise + affine (+ AdaIN)):
+//
+//   mk_seg_sums    out[s][0][c] = sum_{r in s} (a[r,c] - sa[s,c])
+//                  out[s][1][c] = sum_{r in s} (a[r,c] - sa[s,c]) * (b[r,c] - sb[s,c])
+//       forward statistics: a = b = x, sa = sb = K (any value near the mean: the shifted
+//       sums do not cancel); backward: a = dy, b = x, sb = mean.
+//   mk_seg_affine  out[r,c] = A[s,c] * a[r,c] + B[s,c] * b[r,c] + C[s,c],  s = seg[r]
+//       forward: y = A x + C; backward: dx = A dy + B x + C.
+// A segment is a batch item (instance norms; seg = batch row of every voxel) or the whole
+// tensor (batch norm; seg == NULL).  Sums are fp32 (fp64 for fp64 features), flushed with
+// one atomic per (CTA, segment change, channel); both kernels stream rows with 16-byte
+// accesses, grid = a multiple of the SM count, and are HBM-bound (algorithmic bytes:
+// N*C*b read for the sums, 2*N*C*b for the affine map with one input).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace mk {
+namespace {
+
+constexpr int kNormThreads = 256;
+
+template <typename T> struct Vec16 { static constexpr int n = 16 / sizeof(T); };
+
+template <typename T, int V>
+__device__ __forceinline__ void load_vec(const T *p, typename Acc<T>::type (&v)[V]) {
+  union { uint4 u; T t[V]; } raw;
+  raw.u = __ldg(reinterpret_cast<const uint4 *>(p));
+#pragma unroll
+  for (int i = 0; i < V; ++i) v[i] = to_acc<T>(raw.t[i]);
+}
+
+template <typename T, int V>
+__device__ __forceinline__ void store_vec(T *p, const typename Acc<T>::type (&v)[V]) {
+  union { uint4 u; T t[V]; } raw;
+#pragma unroll
+  for (int i = 0; i < V; ++i) raw.t[i] = from_acc<T, typename Acc<T>::type>(v[i]);
+  *reinterpret_cast<uint4 *>(p) = raw.u;
+}
+
+// Vector path: c % V == 0, 16-byte aligned rows.  Thread (tx, ty): channel vector tx of rows
+// row0 + ty, row0 + ty + TY, ...; a CTA owns `rows_per_cta` consecutive rows.
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+k_seg_sums_vec(const T *__restrict__ a, const T *__restrict__ b, const typename Acc<T>::type *__restrict__ sa,
+               const typename Acc<T>::type *__restrict__ sb, const int32_t *__restrict__ seg, int64_t n, int c,
+               int tx_n, int64_t rows_per_cta, typename Acc<T>::type *__restrict__ out) {
+  using A = typename Acc<T>::type;
+  constexpr int V = Vec16<T>::n;
+  const int tx = threadIdx.x % tx_n, ty = threadIdx.x / tx_n, ty_n = kNormThreads / tx_n;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t r1 = min(n, r0 + rows_per_cta);
+  const int ch = tx * V;
+  const bool active = ch < c;
+  __shared__ A red[2][kNormThreads * V];
+  A s0[V], s1[V], va[V], vb[V], ka[V], kb[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) { s0[i] = 0; s1[i] = 0; ka[i] = 0; kb[i] = 0; }
+  int cur = -1;
+  auto flush = [&]() {
+    if (cur < 0) return;
+    A *o = out + (size_t)cur * 2 * c + ch;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      atomicAdd(o + i, s0[i]);
+      atomicAdd(o + c + i, s1[i]);
+      s0[i] = 0; s1[i] = 0;
+    }
+  };
+  if (active) {
+    for (int64_t r = r0 + ty; r < r1; r += ty_n) {
+      const int s = seg ? __ldg(seg + r) : 0;
+      if (s != cur) {
+        flush();   // a segment boundary inside the CTA's range (rare: rows of a batch item are contiguous)
+        cur = s;
+        if (s >= 0) {
+#pragma unroll
+          for (int i = 0; i < V; ++i) {
+            ka[i] = sa ? sa[(size_t)s * c + ch + i] : (A)0;
+            kb[i] = sb ? sb[(size_t)s * c + ch + i] : (A)0;
+          }
+        }
+      }
+      if (s < 0) continue;
+      load_vec<T, V>(a + (size_t)r * c + ch, va);
+      if (b == a) {
+#pragma unroll
+        for (int i = 0; i < V; ++i) vb[i] = va[i];
+      } else {
+        load_vec<T, V>(b + (size_t)r * c + ch, vb);
+      }
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const A x = va[i] - ka[i];
+        s0[i] += x;
+        s1[i] += x * (vb[i] - kb[i]);
+      }
+    }
+  }
+  // the CTA's partial sums of its last segment are added up in shared memory first: one
+  // atomic per (CTA, channel) instead of one per thread
+  const int last = r1 > r0 ? (seg ? __ldg(seg + (r1 - 1)) : 0) : -1;
+  if (active && cur != last) { flush(); cur = -1; }
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    red[0][threadIdx.x * V + i] = (active && cur == last) ? s0[i] : (A)0;
+    red[1][threadIdx.x * V + i] = (active && cur == last) ? s1[i] : (A)0;
+  }
+  __syncthreads();
+  if (ty == 0 && active && last >= 0) {
+    A *o = out + (size_t)last * 2 * c + ch;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      A t0 = 0, t1 = 0;
+      for (int y = 0; y < ty_n; ++y) {
+        t0 += red[0][(y * tx_n + tx) * V + i];
+        t1 += red[1][(y * tx_n + tx) * V + i];
+      }
+      atomicAdd(o + i, t0);
+      atomicAdd(o + c + i, t1);
+    }
+  }
+}
+
+// Scalar path (any c, any alignment): one thread per (row slot, channel)
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+k_seg_sums_scalar(const T *__restrict__ a, const T *__restrict__ b, const typename Acc<T>::type *__restrict__ sa,
+                  const typename Acc<T>::type *__restrict__ sb, const int32_t *__restrict__ seg, int64_t n, int c,
+                  int64_t rows_per_cta, typename Acc<T>::type *__restrict__ out) {
+  using A = typename Acc<T>::type;
+  const int tx_n = min(c, kNormThreads);
+  const int ty_n = kNormThreads / tx_n;
+  const int tx = threadIdx.x % tx_n, ty = threadIdx.x / tx_n;
+  if (ty >= ty_n) return;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t r1 = min(n, r0 + rows_per_cta);
+  for (int ch = tx; ch < c; ch += tx_n) {
+    A s0 = 0, s1 = 0, ka = 0, kb = 0;
+    int cur = -1;
+    for (int64_t r = r0 + ty; r < r1; r += ty_n) {
+      const int s = seg ? __ldg(seg + r) : 0;
+      if (s != cur) {
+        if (cur >= 0) { atomicAdd(out + (size_t)cur * 2 * c + ch, s0); atomicAdd(out + (size_t)cur * 2 * c + c + ch, s1); }
+        s0 = 0; s1 = 0; cur = s;
+        if (s >= 0) { ka = sa ? sa[(size_t)s * c + ch] : (A)0; kb = sb ? sb[(size_t)s * c + ch] : (A)0; }
+      }
+      if (s < 0) continue;
+      const A x = to_acc<T>(a[(size_t)r * c + ch]) - ka;
+      s0 += x;
+      s1 += x * (to_acc<T>(b[(size_t)r * c + ch]) - kb);
+    }
+    if (cur >= 0) { atomicAdd(out + (size_t)cur * 2 * c + ch, s0); atomicAdd(out + (size_t)cur * 2 * c + c + ch, s1); }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+k_seg_affine_vec(const T *__restrict__ a, const T *__restrict__ b, const int32_t *__restrict__ seg, int64_t n, int c,
+                 const typename Acc<T>::type *__restrict__ ca, const typename Acc<T>::type *__restrict__ cb,
+                 const typename Acc<T>::type *__restrict__ cc, T *__restrict__ out) {
+  using A = typename Acc<T>::type;
+  constexpr int V = Vec16<T>::n;
+  const int vec_per_row = c / V;
+  const int64_t total = n * vec_per_row;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = e / vec_per_row;
+    const int ch = (int)(e - r * vec_per_row) * V;
+    const int s = seg ? __ldg(seg + r) : 0;
+    A va[V], vb[V], o[V];
+    load_vec<T, V>(a + (size_t)r * c + ch, va);
+    if (cb) load_vec<T, V>(b + (size_t)r * c + ch, vb);
+    if (s < 0) {
+#pragma unroll
+      for (int i = 0; i < V; ++i) o[i] = 0;
+    } else {
+      const A *pa = ca + (size_t)s * c + ch, *pc = cc + (size_t)s * c + ch;
+#pragma unroll
+      for (int i = 0; i < V; ++i) o[i] = __ldg(pa + i) * va[i] + __ldg(pc + i);
+      if (cb) {
+        const A *pb = cb + (size_t)s * c + ch;
+#pragma unroll
+        for (int i = 0; i < V; ++i) o[i] += __ldg(pb + i) * vb[i];
+      }
+    }
+    store_vec<T, V>(out + (size_t)r * c + ch, o);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+k_seg_affine_scalar(const T *__restrict__ a, const T *__restrict__ b, const int32_t *__restrict__ seg, int64_t n,
+                    int c, const typename Acc<T>::type *__restrict__ ca, const typename Acc<T>::type *__restrict__ cb,
+                    const typename Acc<T>::type *__restrict__ cc, T *__restrict__ out) {
+  using A = typename Acc<T>::type;
+  const int64_t total = n * c;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = e / c;
+    const int ch = (int)(e - r * c);
+    const int s = seg ? __ldg(seg + r) : 0;
+    A o = 0;
+    if (s >= 0) {
+      o = ca[(size_t)s * c + ch] * to_acc<T>(a[e]) + cc[(size_t)s * c + ch];
+      if (cb) o += cb[(size_t)s * c + ch] * to_acc<T>(b[e]);
+    }
+    out[e] = from_acc<T, A>(o);
+  }
+}
+
+template <typename T>
+int seg_sums_t(const void *a, const void *b, const void *sa, const void *sb, const int32_t *seg, int64_t n, int c,
+               int64_t n_seg, void *out, cudaStream_t st) {
+  using A = typename Acc<T>::type;
+  MK_CUDA(cudaMemsetAsync(out, 0, (size_t)n_seg * 2 * c * sizeof(A), st));
+  if (n == 0) return MK_OK;
+  constexpr int V = Vec16<T>::n;
+  // enough CTAs to fill the machine, each with a long enough row range to amortise its flush
+  const int64_t ctas = std::max<int64_t>(1, std::min<int64_t>((int64_t)num_sms() * 8, ceil_div(n, 64)));
+  const int64_t rows_per_cta = ceil_div(n, ctas);
+  const unsigned grid = (unsigned)ceil_div(n, rows_per_cta);
+  const bool vec = c % V == 0 && c / V <= kNormThreads && ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0;
+  if (vec) {
+    int tx_n = 1;
+    while (tx_n < c / V) tx_n <<= 1;
+    k_seg_sums_vec<T><<<grid, kNormThreads, 0, st>>>((const T *)a, (const T *)b, (const A *)sa, (const A *)sb, seg, n, c,
+                                                     tx_n, rows_per_cta, (A *)out);
+  } else {
+    k_seg_sums_scalar<T><<<grid, kNormThreads, 0, st>>>((const T *)a, (const T *)b, (const A *)sa, (const A *)sb, seg, n,
+                                                        c, rows_per_cta, (A *)out);
+  }
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+template <typename T>
+int seg_affine_t(const void *a, const void *b, const int32_t *seg, int64_t n, int c, const void *ca, const void *cb,
+                 const void *cc, void *out, cudaStream_t st) {
+  using A = typename Acc<T>::type;
+  if (n == 0) return MK_OK;
+  constexpr int V = Vec16<T>::n;
+  const bool vec = c % V == 0 && ((uintptr_t)a & 15) == 0 && ((uintptr_t)out & 15) == 0 && (!cb || ((uintptr_t)b & 15) == 0);
+  const int64_t total = vec ? n * (c / V) : n * c;
+  const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(ceil_div(total, kNormThreads), (int64_t)num_sms() * 16));
+  if (vec)
+    k_seg_affine_vec<T><<<grid, kNormThreads, 0, st>>>((const T *)a, (const T *)b, seg, n, c, (const A *)ca, (const A *)cb,
+                                                       (const A *)cc, (T *)out);
+  else
+    k_seg_affine_scalar<T><<<grid, kNormThreads, 0, st>>>((const T *)a, (const T *)b, seg, n, c, (const A *)ca,
+                                                          (const A *)cb, (const A *)cc, (T *)out);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+}  // namespace
+}  // namespace mk
+
+using namespace mk;
+
+extern "C" {
+
+int mk_seg_sums(int dtype, const void *a, const void *b, const void *shift_a, const void *shift_b,
+                const int32_t *seg_of_row, int64_t n, int c, int64_t n_seg, void *out, void *stream) {
+  MK_CHECK_ARG(n >= 0 && c >= 1 && n_seg >= 1, "bad sizes");
+  MK_CHECK_ARG(out && (n == 0 || (a && b)), "null pointer");
+  MK_DISPATCH_DTYPE(dtype, return seg_sums_t<T>(a, b, shift_a, shift_b, seg_of_row, n, c, n_seg, out,
+                                                (cudaStream_t)stream));
+  return MK_OK;
+}
+
+int mk_seg_affine(int dtype, const void *a, const void *b, const int32_t *seg_of_row, int64_t n, int c,
+                  const void *coef_a, const void *coef_b, const void *coef_c, void *out, void *stream) {
+  MK_CHECK_ARG(n >= 0 && c >= 1, "bad sizes");
+  MK_CHECK_ARG(n == 0 || (a && out && coef_a && coef_c && (!coef_b || b)), "null pointer");
+  MK_DISPATCH_DTYPE(dtype, return seg_affine_t<T>(a, b, seg_of_row, n, c, coef_a, coef_b, coef_c, out,
+                                                  (cudaStream_t)stream));
+  return MK_OK;
+}
+
+}  // extern "C"

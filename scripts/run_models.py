@@ -26,9 +26,21 @@ def timed(fn, n=3):
 
 def profile(step, tag):
     from torch.profiler import ProfilerActivity, profile as tprofile
+    from mink_octtree_stablediffusion_b200 import backend_ops
+    backend_ops.CONV_LOG = []
     with tprofile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
         step()
         torch.cuda.synchronize()
+    log, backend_ops.CONV_LOG = backend_ops.CONV_LOG, None
+    kern = sorted(((e.time_range.start, e.time_range.elapsed_us(), e.name) for e in prof.events()
+                   if e.device_type.name == "CUDA" and ("k_conv_tc" in e.name or "k_conv_wgrad_tc" in e.name
+                                                         or "k_conv_fwd_simt" in e.name or "k_conv_wgrad_simt" in e.name)))
+    print(f"[{tag}] conv launches: {len(kern)} kernels, {len(log)} calls")
+    if len(kern) == len(log):
+        for (t0, us, name), rec in zip(kern, log):
+            kind, n_out, n_in, K, ci, co, dt, ordered = rec
+            print(f"  {us:9.1f} us  {kind:5s} n_out={n_out:8d} n_in={n_in:8d} K={K:3d} {ci:4d}->{co:4d} {dt[6:]:8s} "
+                  f"{'ordered' if ordered else 'plain  '} {name[:28]}")
     ev = prof.key_averages()
     rows = sorted(((e.device_time_total, e.count, e.key) for e in ev if e.device_time_total > 0 and e.device_type.name == "CUDA"),
                   reverse=True)
@@ -47,17 +59,17 @@ def run_vae(a):
     torch.manual_seed(0)
     model, plm, m = W.load_vae(cfg)
     plm = plm.cuda()
-    if a.dtype == "bf16":
-        plm = plm.to(torch.bfloat16)
     plm.train()
     opt = plm.configure_optimizers()
+    amp = torch.autocast("cuda", dtype=torch.bfloat16, enabled=a.dtype == "bf16")
     coords = torch.from_numpy(W.batched(W.g3_batch(a.res, a.batch))).cuda()
     print(f"[vae] res {a.res} batch {a.batch}: {len(coords)} voxels", flush=True)
     batch = {"coords": coords}
 
     def step():
         opt.zero_grad(set_to_none=True)
-        loss = plm.training_step(batch, 0)
+        with amp:
+            loss = plm.training_step(batch, 0)
         loss.backward()
         opt.step()
         return loss
@@ -68,6 +80,17 @@ def run_vae(a):
     print("[vae] step times (s):", [round(t, 4) for t in ts], "logged", {k: round(float(v), 5) for k, v in plm._logged.items()})
     if a.profile:
         profile(step, "vae")
+    if a.cprofile:
+        import cProfile
+        import pstats
+        pr = cProfile.Profile()
+        pr.enable()
+        step()
+        torch.cuda.synchronize()
+        pr.disable()
+        st = pstats.Stats(pr)
+        st.sort_stats("cumulative").print_stats(45)
+        st.sort_stats("tottime").print_stats(30)
 
 
 def run_minkunet(a):
@@ -133,6 +156,7 @@ if __name__ == "__main__":
     pa.add_argument("--radius", type=int, default=40)
     pa.add_argument("--dtype", default="fp32")
     pa.add_argument("--profile", action="store_true")
+    pa.add_argument("--cprofile", action="store_true")
     pa.add_argument("--unet_channel", type=int, nargs=4, default=(4, 320, 640, 960))
     a = pa.parse_args()
     rc = 0
