@@ -49,43 +49,30 @@ def _fused_batch_norm(bn: torch.nn.modules.batchnorm._BatchNorm, x: torch.Tensor
     """Training-mode batch norm of the feature matrix (statistics over all rows; for
     SyncBatchNorm over the rows of all ranks), running statistics updated like torch's
     (`momentum`, unbiased running variance).  Returns None when the case is not served
-    (eval mode, no rows) and the caller uses torch's own."""
-    from mink_octtree_stablediffusion_b200.backend_norm import segment_norm
+    (eval mode, no rows, parameters not of the accumulator dtype) and the caller uses torch's own."""
+    from mink_octtree_stablediffusion_b200.backend_norm import batch_norm_train
     use_batch_stats = bn.training or not bn.track_running_stats or bn.running_mean is None
     if not use_batch_stats or x.shape[0] == 0 or not x.is_floating_point():
         return None
     acc = _acc(x)
-    n = x.shape[0]
-    counts = torch.full((1,), float(n), dtype=acc, device=x.device)
+    tensors = [t for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var) if t is not None]
+    if any(t.dtype != acc or t.device != x.device for t in tensors):
+        return None
     reduce_fn = None
     if sync_group is not False:
         import torch.distributed as dist
         group = sync_group
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-            def reduce_fn(sums, cnt):
-                flat = sums.reshape(-1) if cnt is None else torch.cat([sums.reshape(-1), cnt.reshape(-1).to(sums.dtype)])
+            def reduce_fn(flat):
                 dist.all_reduce(flat, group=group)
-                if cnt is None:
-                    return flat.view_as(sums), None
-                return flat[:sums.numel()].view_as(sums), flat[sums.numel():].view_as(cnt)
-    # centre of the one-pass sums: the running mean when ranks must agree on it, else the first row
-    if reduce_fn is not None:
-        shift = (bn.running_mean.detach().to(acc).view(1, -1).contiguous() if bn.running_mean is not None
-                 else torch.zeros((1, x.shape[1]), dtype=acc, device=x.device))
-    else:
-        shift = x[:1].detach().to(acc).contiguous()
-    stats = []
-    y = segment_norm(x, None, 1, counts, _bn_coef(bn.eps), (bn.weight, bias_or_none(bn)), shift=shift,
-                     reduce_fn=reduce_fn, stats_out=stats)
-    if bn.training and bn.track_running_stats and bn.running_mean is not None:
-        mean, var, m = stats[0]
-        with torch.no_grad():
-            bn.num_batches_tracked.add_(1)
-            f = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
-            unbiased = var * (m / (m - 1).clamp(min=1))
-            bn.running_mean.mul_(1 - f).add_(mean.view(-1).to(bn.running_mean.dtype), alpha=f)
-            bn.running_var.mul_(1 - f).add_(unbiased.view(-1).to(bn.running_var.dtype), alpha=f)
-    return y
+    track = bn.training and bn.track_running_stats and bn.running_mean is not None
+    momentum = None
+    if track:
+        bn.num_batches_tracked.add_(1)
+        # momentum=None is torch's cumulative average (needs the step count on the host)
+        momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+    return batch_norm_train(x, bn.weight, bias_or_none(bn), bn.running_mean if track else None,
+                            bn.running_var if track else None, momentum, bn.eps, reduce_fn)
 
 
 def bias_or_none(bn):

@@ -335,6 +335,21 @@ int mk_seg_affine(int dtype, const void *a, const void *b,
                   const void *coef_a, const void *coef_b, const void *coef_c,
                   void *out, void *stream);
 
+/* Batch-norm coefficients between the two passes, one launch each (torch.nn.BatchNorm1d semantics,
+ * MinkowskiNormalization.py:55-103).  All arrays are [c] of the accumulator type (float, or double
+ * when acc_f64); the row count m is count_dev[0] (SyncBatchNorm: all-reduced on the device) or
+ * count_host.
+ *   fwd: sums = mk_seg_sums(x, x, shift, shift) -> mean, invstd, y = coef_a x + coef_c, and, when
+ *        running_mean / running_var are given, r = (1 - momentum) r + momentum {mean, unbiased var}
+ *   bwd: sums = mk_seg_sums(dy, x, NULL, mean)  -> dx = coef_a dy + coef_b x + coef_c, dweight, dbias */
+int mk_bn_coef_fwd(int acc_f64, const void *sums, const void *shift, const void *count_dev, double count_host,
+                   const void *weight, const void *bias, double eps, int c, void *coef_a, void *coef_c,
+                   void *mean_out, void *invstd_out, void *running_mean, void *running_var, double momentum,
+                   void *stream);
+int mk_bn_coef_bwd(int acc_f64, const void *sums, const void *mean, const void *invstd, const void *count_dev,
+                   double count_host, const void *weight, int c, void *coef_a, void *coef_b, void *coef_c,
+                   void *dweight, void *dbias, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

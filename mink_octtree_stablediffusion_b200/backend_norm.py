@@ -119,3 +119,85 @@ def segment_norm(x: torch.Tensor, seg: Optional[torch.Tensor], n_seg: int, count
     to centre the one-pass sums; reduce_fn(sums, counts) -> (sums, counts) all-reduces them over ranks;
     stats_out (optional list) receives (mean, var, count) for running-statistics updates."""
     return _SegmentNorm.apply(x, seg, n_seg, counts, shift, coef_fn, reduce_fn, stats_out, *params)
+
+
+# ---------------------------------------------------------------------------
+# batch norm: the same two passes with the [C]-sized algebra in one launch each
+# ---------------------------------------------------------------------------
+def _seg_sums_into(out, a, b, shift_a, shift_b):
+    lib = _lib.load()
+    n, c = a.shape
+    _lib.check(lib.mk_seg_sums(_dtype_code(a), _ptr(a), _ptr(b), _ptr(shift_a), _ptr(shift_b), None, n, c, 1,
+                               ctypes.c_void_p(out.data_ptr()), _stream()))
+
+
+class _BatchNormTrain(torch.autograd.Function):
+    """y = batch_norm(x) with batch statistics (torch.nn.BatchNorm1d in training mode,
+    MinkowskiNormalization.py:55-103); `reduce_fn` makes the statistics global (SyncBatchNorm)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, reduce_fn):
+        lib = _lib.load()
+        x = x.contiguous()
+        n, c = x.shape
+        acc = _acc_dtype(x)
+        f64 = int(acc == torch.float64)
+        dev = x.device
+        buf = torch.empty((7, c), dtype=acc, device=dev)      # sums[2], A, C, mean, invstd, shift
+        sums, coef_a, coef_c, mean, invstd, shift = buf[0:2], buf[2], buf[3], buf[4], buf[5], buf[6]
+        count_dev = None
+        if reduce_fn is None:
+            shift.copy_(x[0])                                 # any value near the mean centres the one-pass sums
+        elif running_mean is not None:
+            shift.copy_(running_mean)                         # ... the same one on every rank
+        else:
+            shift.zero_()
+        _seg_sums_into(sums, x, x, shift, shift)
+        if reduce_fn is not None:
+            flat = torch.cat([sums.reshape(-1), torch.full((1,), float(n), dtype=acc, device=dev)])
+            reduce_fn(flat)
+            sums = flat[:2 * c].view(2, c)
+            count_dev = flat[2 * c:]
+        upd = running_mean is not None and momentum is not None
+        _lib.check(lib.mk_bn_coef_fwd(f64, _ptr(sums), _ptr(shift), _ptr(count_dev), float(n), _ptr(weight), _ptr(bias),
+                                      float(eps), c, _ptr(coef_a), _ptr(coef_c), _ptr(mean), _ptr(invstd),
+                                      _ptr(running_mean) if upd else None, _ptr(running_var) if upd else None,
+                                      float(momentum or 0.0), _stream()))
+        y = seg_affine(x, None, None, coef_a, None, coef_c)
+        ctx.save_for_backward(x, weight, mean, invstd, count_dev if count_dev is not None else torch.empty(0))
+        ctx.reduce_fn, ctx.n = reduce_fn, n
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, weight, mean, invstd, count_dev = ctx.saved_tensors
+        dy = dy.contiguous()
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        n, c = x.shape
+        acc = mean.dtype
+        buf = torch.empty((7, c), dtype=acc, device=x.device)  # sums[2], cA, cB, cC, dweight, dbias
+        sums = buf[0:2]
+        _seg_sums_into(sums, dy, x, None, mean)
+        if ctx.reduce_fn is not None:
+            ctx.reduce_fn(sums)
+        _lib.check(lib.mk_bn_coef_bwd(int(acc == torch.float64), _ptr(sums), _ptr(mean), _ptr(invstd),
+                                      _ptr(count_dev) if count_dev.numel() else None, float(ctx.n), _ptr(weight), c,
+                                      _ptr(buf[2]), _ptr(buf[3]), _ptr(buf[4]), _ptr(buf[5]), _ptr(buf[6]), _stream()))
+        dx = seg_affine(dy, x, None, buf[2], buf[3], buf[4])
+        # under SyncBatchNorm sums are global; the parameter gradients a rank reports are its LOCAL share in
+        # torch's implementation, and DDP sums them - the global value divided by the world size keeps that sum
+        dw, db = buf[5], buf[6]
+        if ctx.reduce_fn is not None:
+            import torch.distributed as dist
+            w = dist.get_world_size()
+            dw, db = dw / w, db / w
+        return (dx, dw if weight is not None else None, db if ctx.has_bias else None, None, None, None, None, None)
+
+
+def batch_norm_train(x, weight, bias, running_mean, running_var, momentum, eps, reduce_fn=None):
+    """weight / bias / running statistics must be of the accumulator dtype (float32, or float64 for
+    float64 features); reduce_fn(flat_tensor) all-reduces in place."""
+    return _BatchNormTrain.apply(x, weight, bias, running_mean, running_var, momentum, eps, reduce_fn)

@@ -215,6 +215,56 @@ k_seg_affine_scalar(const T *__restrict__ a, const T *__restrict__ b, const int3
   }
 }
 
+// Batch-norm coefficient kernels: the [C]-sized algebra between the two passes as ONE launch each
+// (as torch ops it is ~40 tiny launches per layer and dominated the host time of the VAE step).
+//   forward : S = sums of (x - K), (x - K)^2 over m rows  ->  mean, invstd, y = A x + C coefficients,
+//             running statistics (momentum f, unbiased variance) as torch.nn.BatchNorm1d keeps them
+//   backward: S = sums of dy, dy (x - mean)  ->  dx = cA dy + cB x + cC coefficients, dweight, dbias
+template <typename A>
+__global__ void k_bn_coef_fwd(const A *__restrict__ S, const A *__restrict__ shift, const A *__restrict__ count_dev,
+                              double count_host, const A *__restrict__ weight, const A *__restrict__ bias, double eps,
+                              int c, A *__restrict__ coef_a, A *__restrict__ coef_c, A *__restrict__ mean_out,
+                              A *__restrict__ invstd_out, A *__restrict__ running_mean, A *__restrict__ running_var,
+                              double momentum) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= c) return;
+  const A m = count_dev ? max(count_dev[0], (A)1) : (A)count_host;
+  const A d = S[ch] / m;
+  const A mean = (shift ? shift[ch] : (A)0) + d;
+  A var = S[c + ch] / m - d * d;
+  var = var > (A)0 ? var : (A)0;
+  const A inv = (A)1 / sqrt(var + (A)eps);
+  const A a = weight ? weight[ch] * inv : inv;
+  coef_a[ch] = a;
+  coef_c[ch] = (bias ? bias[ch] : (A)0) - mean * a;
+  mean_out[ch] = mean;
+  invstd_out[ch] = inv;
+  if (running_mean) {
+    const A f = (A)momentum;
+    const A unbiased = var * (m / max(m - (A)1, (A)1));
+    running_mean[ch] = ((A)1 - f) * running_mean[ch] + f * mean;
+    running_var[ch] = ((A)1 - f) * running_var[ch] + f * unbiased;
+  }
+}
+
+template <typename A>
+__global__ void k_bn_coef_bwd(const A *__restrict__ S, const A *__restrict__ mean, const A *__restrict__ invstd,
+                              const A *__restrict__ count_dev, double count_host, const A *__restrict__ weight, int c,
+                              A *__restrict__ coef_a, A *__restrict__ coef_b, A *__restrict__ coef_c,
+                              A *__restrict__ dweight, A *__restrict__ dbias) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= c) return;
+  const A m = count_dev ? max(count_dev[0], (A)1) : (A)count_host;
+  const A s0 = S[ch], s1 = S[c + ch], inv = invstd[ch], w = weight ? weight[ch] : (A)1;
+  const A a = w * inv;
+  const A b = -w * inv * inv * inv * s1 / m;
+  coef_a[ch] = a;
+  coef_b[ch] = b;
+  coef_c[ch] = -a * s0 / m - b * mean[ch];
+  if (dweight) dweight[ch] = inv * s1;
+  if (dbias) dbias[ch] = s0;
+}
+
 template <typename T>
 int seg_sums_t(const void *a, const void *b, const void *sa, const void *sb, const int32_t *seg, int64_t n, int c,
                int64_t n_seg, void *out, cudaStream_t st) {
@@ -281,6 +331,45 @@ int mk_seg_affine(int dtype, const void *a, const void *b, const int32_t *seg_of
   MK_CHECK_ARG(n == 0 || (a && out && coef_a && coef_c && (!coef_b || b)), "null pointer");
   MK_DISPATCH_DTYPE(dtype, return seg_affine_t<T>(a, b, seg_of_row, n, c, coef_a, coef_b, coef_c, out,
                                                   (cudaStream_t)stream));
+  return MK_OK;
+}
+
+int mk_bn_coef_fwd(int acc_f64, const void *sums, const void *shift, const void *count_dev, double count_host,
+                   const void *weight, const void *bias, double eps, int c, void *coef_a, void *coef_c,
+                   void *mean_out, void *invstd_out, void *running_mean, void *running_var, double momentum,
+                   void *stream) {
+  MK_CHECK_ARG(c >= 1 && sums && coef_a && coef_c && mean_out && invstd_out, "bad arguments");
+  MK_CHECK_ARG((running_mean == nullptr) == (running_var == nullptr), "running statistics come in pairs");
+  const unsigned grid = (unsigned)ceil_div(c, 128);
+  if (acc_f64)
+    k_bn_coef_fwd<double><<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const double *)sums, (const double *)shift, (const double *)count_dev, count_host, (const double *)weight,
+        (const double *)bias, eps, c, (double *)coef_a, (double *)coef_c, (double *)mean_out, (double *)invstd_out,
+        (double *)running_mean, (double *)running_var, momentum);
+  else
+    k_bn_coef_fwd<float><<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const float *)sums, (const float *)shift, (const float *)count_dev, count_host, (const float *)weight,
+        (const float *)bias, eps, c, (float *)coef_a, (float *)coef_c, (float *)mean_out, (float *)invstd_out,
+        (float *)running_mean, (float *)running_var, momentum);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+int mk_bn_coef_bwd(int acc_f64, const void *sums, const void *mean, const void *invstd, const void *count_dev,
+                   double count_host, const void *weight, int c, void *coef_a, void *coef_b, void *coef_c,
+                   void *dweight, void *dbias, void *stream) {
+  MK_CHECK_ARG(c >= 1 && sums && mean && invstd && coef_a && coef_b && coef_c, "bad arguments");
+  const unsigned grid = (unsigned)ceil_div(c, 128);
+  if (acc_f64)
+    k_bn_coef_bwd<double><<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const double *)sums, (const double *)mean, (const double *)invstd, (const double *)count_dev, count_host,
+        (const double *)weight, c, (double *)coef_a, (double *)coef_b, (double *)coef_c, (double *)dweight,
+        (double *)dbias);
+  else
+    k_bn_coef_bwd<float><<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const float *)sums, (const float *)mean, (const float *)invstd, (const float *)count_dev, count_host,
+        (const float *)weight, c, (float *)coef_a, (float *)coef_b, (float *)coef_c, (float *)dweight, (float *)dbias);
+  MK_LAUNCH_CHECK();
   return MK_OK;
 }
 

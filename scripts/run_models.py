@@ -76,6 +76,9 @@ def run_vae(a):
 
     loss = step()
     print("[vae] first step loss", float(loss), flush=True)
+    import gc
+    gc.collect()
+    gc.freeze()
     ts = timed(step, a.steps)
     print("[vae] step times (s):", [round(t, 4) for t in ts], "logged", {k: round(float(v), 5) for k, v in plm._logged.items()})
     if a.profile:
