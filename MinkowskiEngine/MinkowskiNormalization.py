@@ -161,7 +161,12 @@ class MinkowskiSyncBatchNorm(MinkowskiBatchNorm):
 
     def forward(self, input):
         x = input.F
-        y = _fused_batch_norm(self.bn, x, sync_group=self.bn.process_group) if x.is_cuda else None
+        # NB `convert_sync_batchnorm` below re-attaches the ORIGINAL BatchNorm1d as `.bn` when it recurses into the
+        # converted module's children - the reference does exactly that (MinkowskiNormalization.py:188-192), so
+        # a converted network normalises with local statistics there and here; a directly constructed
+        # MinkowskiSyncBatchNorm synchronises.
+        group = self.bn.process_group if isinstance(self.bn, torch.nn.SyncBatchNorm) else False
+        y = _fused_batch_norm(self.bn, x, sync_group=group) if x.is_cuda else None
         return _like(input, self.bn(x) if y is None else y)
 
     @classmethod

@@ -160,7 +160,8 @@ def run_engine(args):
         raise SystemExit("bench.py: no CUDA device; this engine has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=180))
     import MinkowskiEngine as ME
     import MinkowskiEngineBackend._C as _C
     from mink_octtree_stablediffusion_b200 import _lib
@@ -518,11 +519,14 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
         rec = {"steps_per_s": 1e3 / ms, "ms_per_step": ms, "samples_per_s": batch * world * 1e3 / ms,
                "voxels_per_s": n_vox * world * 1e3 / ms, "loss": float(loss), "engine_launches_per_step":
                (int(lib.mk_launch_count()) - l0) // steps}
-        if rank == 0 and not args.no_vae_profile:
+        if not args.no_vae_profile:
+            # one more step on EVERY rank (it holds collectives); rank 0 records its kernels
+            import contextlib
             from torch.profiler import ProfilerActivity, profile as tprofile
-            with tprofile(activities=[ProfilerActivity.CUDA]) as prof:
+            with (tprofile(activities=[ProfilerActivity.CUDA]) if rank == 0 else contextlib.nullcontext()) as prof:
                 step()
                 torch.cuda.synchronize()
+        if rank == 0 and not args.no_vae_profile:
             split = {}
             for e in prof.key_averages():
                 if e.device_time_total > 0:
