@@ -108,10 +108,13 @@ def sparse_quantize(coordinates, features=None, labels=None, ignore_label=-100, 
     discrete = discrete.astype(np.int32) if isinstance(discrete, np.ndarray) else discrete.int()
     is_np = isinstance(discrete, np.ndarray)
 
-    on_gpu = _is_cuda_device(device) and not use_label
+    # CUDA coordinates (or device="cuda") are de-duplicated by the engine's GPU coordinate hash
+    # (first occurrence kept, ascending: the same maps as the host path)
+    on_gpu = _is_cuda_device(device) or (not is_np and discrete.is_cuda)
     if on_gpu:
         import MinkowskiEngineBackend._C as MEB
-        dev_coords = (torch.from_numpy(discrete) if is_np else discrete).to(device)
+        dev_coords = (torch.from_numpy(discrete) if is_np else discrete)
+        dev_coords = dev_coords if dev_coords.is_cuda else dev_coords.to(device)
         mgr = MEB.CoordinateMapManagerGPU_c10()
         _, (unique_map, inverse_map) = mgr.insert_and_map(dev_coords, [1] * (dimension - 1), "")
         if is_np or not discrete.is_cuda:
@@ -126,7 +129,18 @@ def sparse_quantize(coordinates, features=None, labels=None, ignore_label=-100, 
             unique_map = torch.from_numpy(umap).to(discrete.device)
             inverse_map = torch.from_numpy(imap).to(discrete.device)
 
-    if use_label:
+    if use_label and not is_np and discrete.is_cuda:
+        # label voting on the device: a voxel whose points disagree on the label gets ignore_label
+        lab = labels.to(discrete.device).reshape(-1)
+        first_lab = lab[unique_map]
+        conflict = torch.zeros(len(unique_map), dtype=torch.int32, device=lab.device)
+        conflict.index_put_((inverse_map,), (lab != first_lab[inverse_map]).int(), accumulate=True)
+        colabels = torch.where(conflict > 0, torch.full_like(first_lab, ignore_label), first_lab)
+        ret = [discrete[unique_map]]
+        if use_feat:
+            ret.append(features[unique_map])
+        ret.append(colabels)
+    elif use_label:
         # a voxel whose points disagree on the label gets ignore_label (reference quantize_label_*)
         lab = labels if is_np else labels.cpu().numpy()
         lab = np.asarray(lab).reshape(-1)
