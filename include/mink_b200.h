@@ -86,6 +86,23 @@ int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
                   int32_t *inverse_map, int32_t *coords_out, void *workspace,
                   int64_t *n_unique_dev, int32_t *status_dev, void *stream);
 
+/* mk_map_insert in three launches (four with the inverse map): the table clear also zeroes
+ * the scan state, the dedup / ordered compaction / table update is ONE pass (decoupled
+ * look-back scan), and the maps can be written as int64 directly (what the Python API
+ * returns, MinkowskiCoordinateManager.py:153-179).  flags:
+ *   MK_INSERT_UNIQUE      the caller guarantees distinct rows (children of distinct octree
+ *                         parents - extern.hpp:151-165 with kernel 2 / stride 2 -, pruned rows
+ *                         of a map - extern.hpp:411-419): no dedup pass, ids = row numbers
+ *   MK_INSERT_INT64_MAPS  unique_index / inverse_map are int64 [n]
+ * Same outputs as mk_map_insert otherwise (tested against it). */
+#define MK_INSERT_UNIQUE 1
+#define MK_INSERT_INT64_MAPS 2
+int64_t mk_insert2_workspace_bytes(int64_t n);
+int mk_map_insert2(const int32_t *coords, int64_t n, int ncols, void *table,
+                   int64_t capacity, int flags, void *unique_index,
+                   void *inverse_map, int32_t *coords_out, void *workspace,
+                   int64_t *n_unique_dev, int32_t *status_dev, void *stream);
+
 /* rows[i] = compact row id of query[i] in the table, or -1.
  * Replaces thrust find_coordinate. */
 int mk_map_lookup(const void *table, int64_t capacity, const int32_t *query,
@@ -165,6 +182,14 @@ int64_t mk_kmap_pairs_workspace_bytes(int64_t n_out, int K);
 int mk_kmap_pairs(const int32_t *nbr, int64_t n_out, int64_t ld, int K,
                   int64_t *starts_dev, int32_t *in_rows, int32_t *out_rows,
                   void *workspace, void *stream);
+
+/* Octree split: kernel map of a generative transposed convolution whose kernel equals its
+ * stride (extern.hpp:151-165 with expand_coordinates = true; modules/vae_block.py:279-296),
+ * where the child rows are i*K + k by construction: the table, its inverse (dense), the tile
+ * order and the tile-ordered table are written in closed form, no probes.  Any output may be NULL. */
+int mk_kmap_children(int64_t n_in, int K, int64_t ld_out, int64_t ld_in,
+                     int32_t *nbr, int32_t *inv, int32_t *order,
+                     int32_t *nbr_ordered, void *stream);
 
 /* Per 128-row tile of the table, a K-bit mask of the offsets that have at
  * least one neighbour in the tile: mask[tile * W + k/32] bit (k%32), with

@@ -17,6 +17,7 @@ LIB_PATH = _PKG / "lib" / "libmink_b200.so"
 MK_F32, MK_F64, MK_BF16, MK_F16 = 0, 1, 2, 3
 MK_POOL_SUM, MK_POOL_AVG, MK_POOL_MAX = 0, 1, 2
 MK_BCAST_ADD, MK_BCAST_MUL = 0, 1
+MK_INSERT_UNIQUE, MK_INSERT_INT64_MAPS = 1, 2
 
 _p = C.c_void_p
 _i64 = C.c_int64
@@ -31,6 +32,8 @@ PROTOTYPES = {
     "mk_hash_capacity": (_i64, [_i64]),
     "mk_insert_workspace_bytes": (_i64, [_i64]),
     "mk_map_insert": (_i, [_p, _i64, _i, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "mk_insert2_workspace_bytes": (_i64, [_i64]),
+    "mk_map_insert2": (_i, [_p, _i64, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _p, _p]),
     "mk_map_lookup": (_i, [_p, _i64, _p, _i64, _i, _p, _p]),
     "mk_coords_stride": (_i, [_p, _i64, _i, _p, _p, _p]),
     "mk_coords_expand": (_i, [_p, _i64, _i, _p, _i, _p, _p]),
@@ -43,6 +46,7 @@ PROTOTYPES = {
     "mk_rows_scatter": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "mk_kmap_build": (_i, [_p, _i64, _i, _p, _i64, _p, _i, _p, _i64, _p, _p]),
     "mk_kmap_invert": (_i, [_p, _i64, _i64, _i, _p, _i64, _i64, _p]),
+    "mk_kmap_children": (_i, [_i64, _i, _i64, _i64, _p, _p, _p, _p, _p]),
     "mk_kmap_pairs_workspace_bytes": (_i64, [_i64, _i]),
     "mk_kmap_pairs": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _p]),
     "mk_conv_workspace_bytes": (_i64, [_i, _i64, _i, _i, _i]),

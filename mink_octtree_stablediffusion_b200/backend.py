@@ -218,7 +218,7 @@ class CoordinateMapKey:
 # ---------------------------------------------------------------------------
 class _CoordMap:
     """coordinates [n, D+1] int32 + the hash table over them."""
-    __slots__ = ("coords", "table", "capacity", "n", "tensor_stride", "batch")
+    __slots__ = ("coords", "table", "capacity", "n", "tensor_stride", "batch", "on_grid")
 
     def __init__(self, coords, table, capacity, tensor_stride):
         self.coords = coords
@@ -227,6 +227,7 @@ class _CoordMap:
         self.n = coords.shape[0]
         self.tensor_stride = list(tensor_stride)
         self.batch = None      # lazily: (batch_of_row int32 [n], n_batch)
+        self.on_grid = None    # every coordinate is a multiple of the tensor stride (None: not checked yet)
 
 
 class _KernelMap:
@@ -309,6 +310,7 @@ class CoordinateMapManagerGPU_c10:
         self._origin_key: Optional[CoordinateMapKey] = None
         self._device: Optional[torch.device] = None
         self._rng = random.Random(0x5eed)
+        self._pending_status: List[torch.Tensor] = []
 
     # -- internals ----------------------------------------------------------
     def _check_device(self, t: torch.Tensor) -> None:
@@ -333,29 +335,50 @@ class CoordinateMapManagerGPU_c10:
             if (ts, cand) not in self._maps:
                 return cand
 
-    def _insert(self, coords: torch.Tensor, want_maps: bool):
-        """Hash-insert + dedup + compact.  Returns (coords_u, table, cap, unique_index, inverse)."""
+    def _insert(self, coords: torch.Tensor, want_maps: bool, unique: bool = False):
+        """Hash-insert + dedup + compact (mk_map_insert2: three launches, maps written as int64).
+        `unique`: the rows are distinct by construction (pruned rows, octree children): no dedup
+        pass and no device-to-host read of the count.
+        Returns (coords_u, table, cap, unique_index, inverse)."""
         lib = self._lib
         n, ncols = coords.shape
         dev = coords.device
         cap = int(lib.mk_hash_capacity(n))
         table = torch.empty(cap * 16, dtype=torch.uint8, device=dev)
-        ws = torch.empty(int(lib.mk_insert_workspace_bytes(n)), dtype=torch.uint8, device=dev)
-        coords_out = torch.empty_like(coords)
-        uniq = torch.empty(n, dtype=torch.int32, device=dev) if want_maps else None
-        inv = torch.empty(n, dtype=torch.int32, device=dev) if want_maps else None
+        ws = torch.empty(int(lib.mk_insert2_workspace_bytes(n)), dtype=torch.uint8, device=dev)
+        coords_out = coords if unique else torch.empty_like(coords)
+        uniq = torch.empty(n, dtype=torch.int64, device=dev) if want_maps else None
+        inv = torch.empty(n, dtype=torch.int64, device=dev) if want_maps else None
         meta = torch.empty(2, dtype=torch.int64, device=dev)   # [n_unique, status(int32 in low half)]
-        _lib.check(lib.mk_map_insert(_ptr(coords), n, ncols, _ptr(table), cap, _ptr(uniq), _ptr(inv),
-                                     _ptr(coords_out), _ptr(ws), ctypes.c_void_p(meta.data_ptr()),
-                                     ctypes.c_void_p(meta.data_ptr() + 8), _stream()))
+        flags = _lib.MK_INSERT_INT64_MAPS | (_lib.MK_INSERT_UNIQUE if unique else 0)
+        _lib.check(lib.mk_map_insert2(_ptr(coords), n, ncols, _ptr(table), cap, flags, _ptr(uniq), _ptr(inv),
+                                      _ptr(coords_out), _ptr(ws), ctypes.c_void_p(meta.data_ptr()),
+                                      ctypes.c_void_p(meta.data_ptr() + 8), _stream()))
+        if unique:
+            # out-of-range coordinates of derived maps cannot occur (the source map was checked); the
+            # status word is still looked at when the map is next synchronised on
+            self._pending_status.append(meta)
+            return coords_out, table, cap, uniq, inv
         host = meta.cpu()                       # the one D2H sync a new map costs
         n_u = int(host[0].item())
         status = int(host[1].item()) & 0xFFFFFFFF
+        self._check_status(status)
+        self._drain_status()
+        return coords_out[:n_u], table, cap, (uniq[:n_u] if want_maps else None), inv
+
+    @staticmethod
+    def _check_status(status: int) -> None:
         if status == 2:
             raise RuntimeError("coordinate out of the packable range: batch in [0, 65534], "
                                "spatial coordinates in [-32768, 32767]")
         _require(status == 0, f"coordinate hash insert failed (status {status})")
-        return coords_out[:n_u], table, cap, (uniq[:n_u] if want_maps else None), inv
+
+    def _drain_status(self) -> None:
+        """Status words of the sync-free inserts issued since the last synchronising one."""
+        if self._pending_status:
+            pend, self._pending_status = self._pending_status, []
+            for st in torch.stack(pend).cpu()[:, 1].tolist():
+                self._check_status(int(st) & 0xFFFFFFFF)
 
     def _register(self, key_tuple, coords_u, table, cap) -> _CoordMap:
         m = _CoordMap(coords_u, table, cap, key_tuple[0])
@@ -363,8 +386,8 @@ class CoordinateMapManagerGPU_c10:
         return m
 
     def _new_map_from_coords(self, coords: torch.Tensor, tensor_stride, string_id: str,
-                             want_maps: bool = False):
-        coords_u, table, cap, uniq, inv = self._insert(coords, want_maps)
+                             want_maps: bool = False, unique: bool = False):
+        coords_u, table, cap, uniq, inv = self._insert(coords, want_maps, unique)
         sid = self._fresh_id(tensor_stride, string_id)
         kt = (tuple(int(s) for s in tensor_stride), sid)
         self._register(kt, coords_u, table, cap)
@@ -382,7 +405,7 @@ class CoordinateMapManagerGPU_c10:
         self._check_device(coordinates)
         coords = coordinates.contiguous()
         key, uniq, inv = self._new_map_from_coords(coords, tensor_stride, string_id, want_maps=True)
-        return key, (uniq.long(), inv.long())
+        return key, (uniq, inv)
 
     def stride(self, in_key: CoordinateMapKey, stride: Sequence[int], string_id: str = "") -> CoordinateMapKey:
         """Strided child map: coordinates floored to multiples of ts*stride and
@@ -409,8 +432,40 @@ class CoordinateMapManagerGPU_c10:
             _lib.check(self._lib.mk_coords_stride(_ptr(m.coords), m.n, m.coords.shape[1], _np_ptr(ts_h),
                                                   _ptr(tmp), _stream()))
             out_key, _, _ = self._new_map_from_coords(tmp, out_ts, sid)
+            self._get(out_key).on_grid = True
         self._stride_maps[cache_key] = out_key
         return out_key
+
+    def _is_on_grid(self, m: _CoordMap) -> bool:
+        """All coordinates of the map are multiples of its tensor stride (true by construction for
+        strided / generated / pruned maps; checked once, with one device read, for inserted ones)."""
+        if m.on_grid is None:
+            ts = torch.tensor(m.tensor_stride, dtype=torch.int32, device=m.coords.device).clamp(min=1)
+            m.on_grid = bool((m.coords[:, 1:] % ts == 0).all().item()) if m.n else True
+        return m.on_grid
+
+    def _octree_children(self, in_key: CoordinateMapKey, offsets: np.ndarray, out_ts: Sequence[int]):
+        """Generative expansion whose offsets stay inside the parent cell (kernel == stride: the
+        octree split of modules/vae_block.py:279-296): the K children of distinct parents cannot
+        collide, so they are inserted without the dedup pass and without reading a count back, and
+        child row i*K + k is known to hang under offset k of parent i.  Returns the new key, or
+        None when the expansion is not of that form (general path: expand + dedup insert)."""
+        m = self._get(in_key)
+        offs = np.asarray(offsets, dtype=np.int64)
+        in_ts = np.asarray(m.tensor_stride, dtype=np.int64)
+        K = len(offs)
+        if K < 2 or m.n == 0 or (offs < 0).any() or (offs >= in_ts[None, :]).any() or len(np.unique(offs, axis=0)) != K:
+            return None
+        if not self._is_on_grid(m):
+            return None
+        ncols = m.coords.shape[1]
+        tmp = torch.empty((m.n * K, ncols), dtype=torch.int32, device=m.coords.device)
+        offs_h = _host_i32(offs)
+        _lib.check(self._lib.mk_coords_expand(_ptr(m.coords), m.n, ncols, _np_ptr(offs_h), K, _ptr(tmp), _stream()))
+        sid = in_key.get_key()[1]
+        key, _, _ = self._new_map_from_coords(tmp, out_ts, self._fresh_id(out_ts, sid + "g" if sid else "g"), unique=True)
+        self._get(key).on_grid = True
+        return key
 
     def _stride_region(self, in_key: CoordinateMapKey, offsets: np.ndarray, out_ts: Sequence[int],
                        expand: bool) -> CoordinateMapKey:
@@ -512,7 +567,7 @@ class CoordinateMapManagerGPU_c10:
         out_key.set_key(key.get_key()[0], key.get_key()[1])
         res, start = [], 0
         for m in maps:
-            rows = inv[start:start + m.n].long()
+            rows = inv[start:start + m.n]
             res.append(torch.stack([torch.arange(m.n, dtype=torch.int64, device=rows.device), rows]))
             start += m.n
         return res

@@ -94,9 +94,11 @@ def _order_table(mgr, table, n_rows, ld, K, coords):
     return order, out, _tile_mask(mgr, out, n_rows, ld, K)
 
 
-def _want_order(mgr, x, n_rows, K, c_in, c_out) -> bool:
+def _want_order(mgr, x, n_rows, K, c_in, c_out, have=False) -> bool:
+    """`have`: the ordered form exists already (octree split: written in closed form), so the size
+    threshold below which building it does not pay is moot."""
     on, n_min, _ = _tile_order_cfg()
-    return (on and n_rows >= n_min and x.dtype in (torch.bfloat16, torch.float16, torch.float32)
+    return (on and (have or n_rows >= n_min) and x.dtype in (torch.bfloat16, torch.float16, torch.float32)
             and bool(mgr._lib.mk_conv_tc_eligible(_dtype_code(x), n_rows, K, c_in, c_out)))
 
 
@@ -151,9 +153,8 @@ def _kernel_map(mgr: CoordinateMapManagerGPU_c10, in_key: CoordinateMapKey, out_
     kernel_size = [int(k) for k in kernel_size]
     kernel_stride = [int(s) for s in kernel_stride]
     kernel_dilation = [int(d) for d in kernel_dilation]
-    cache_key = (in_key._tuple(), out_key._tuple(), tuple(kernel_size), tuple(kernel_stride),
-                 tuple(kernel_dilation), int(region_type), bool(is_transpose), bool(is_pool),
-                 None if offset is None or offset.numel() == 0 else tuple(offset.reshape(-1).tolist()))
+    cache_key = _kmap_cache_key(in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
+                                is_transpose, is_pool)
     km = mgr._kmaps.get(cache_key)
     if km is not None:
         return km
@@ -169,6 +170,39 @@ def _kernel_map(mgr: CoordinateMapManagerGPU_c10, in_key: CoordinateMapKey, out_
         offs = region_offsets(kernel_size, scale, region_type, offset)
         km = _build_table(mgr, out_map, in_map, -offs, False)
     mgr._kmaps[cache_key] = km
+    return km
+
+
+def _kmap_cache_key(in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset, is_transpose,
+                    is_pool):
+    return (in_key._tuple(), out_key._tuple(), tuple(int(k) for k in kernel_size), tuple(int(s) for s in kernel_stride),
+            tuple(int(d) for d in kernel_dilation), int(region_type), bool(is_transpose), bool(is_pool),
+            None if offset is None or offset.numel() == 0 else tuple(offset.reshape(-1).tolist()))
+
+
+def _children_kernel_map(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset):
+    """Transposed kernel map of an octree split (mgr._octree_children): child row i*K + k hangs under
+    offset k of parent i, so the table, its (dense) inverse and the tile-ordered form are written in
+    closed form (mk_kmap_children) and put into the kernel-map cache - no probes, no sort."""
+    in_map, out_map = mgr._get(in_key), mgr._get(out_key)
+    K = out_map.n // max(in_map.n, 1)
+    dev = in_map.coords.device
+    ld_out, ld_in = _pad_ld(out_map.n), _pad_ld(in_map.n)
+    nbr = torch.empty((K, ld_out), dtype=torch.int32, device=dev)
+    inv = torch.empty((K, ld_in), dtype=torch.int32, device=dev)
+    order = torch.empty(out_map.n, dtype=torch.int32, device=dev)
+    nbr_o = torch.empty((K, ld_out), dtype=torch.int32, device=dev)
+    _lib.check(mgr._lib.mk_kmap_children(in_map.n, K, ld_out, ld_in, _ptr(nbr), _ptr(inv), _ptr(order), _ptr(nbr_o),
+                                         _stream()))
+    km = _KernelMap(nbr, ld_out, in_map.n, out_map.n, K, None, False)
+    km.out_coords, km.in_coords = out_map.coords, in_map.coords
+    km._inv = (inv, ld_in)
+    km._ordered = (order, nbr_o, _tile_mask(mgr, nbr_o, out_map.n, ld_out, K))
+    km._imask = _tile_mask(mgr, inv, in_map.n, ld_in, K)
+    km._iordered = (None, inv, km._imask)       # every entry of the inverse is valid: nothing to order
+    for is_pool in (False, True):
+        mgr._kmaps[_kmap_cache_key(in_key, out_key, kernel_size, kernel_stride, kernel_dilation, region_type, offset,
+                                   True, is_pool)] = km
     return km
 
 
@@ -254,7 +288,8 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
     code = _dtype_code(x)
     ws, nbytes = _workspace(lib, code, km.n_out, x.size(0), km.K, c_in, c_out, x.device)
     table, mask, order = km.nbr, None, None
-    if km.n_out > 0 and x.size(0) > 0 and _aligned16(x, dy) and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
+    if (km.n_out > 0 and x.size(0) > 0 and _aligned16(x, dy)
+            and _want_order(mgr, x, km.n_out, km.K, c_in, c_out, km._ordered is not None)):
         # the ordered table pairs column s with dy row order[s]; the kernel reads dy through it
         order, table, mask = _ordered(mgr, km)
     if mask is None:
@@ -268,7 +303,8 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
 
 def _conv_forward(mgr, x, w, km: _KernelMap):
     c_in, c_out = w.size(1), w.size(2)
-    if km.n_out > 0 and x.size(0) > 0 and _aligned16(x) and _want_order(mgr, x, km.n_out, km.K, c_in, c_out):
+    if (km.n_out > 0 and x.size(0) > 0 and _aligned16(x)
+            and _want_order(mgr, x, km.n_out, km.K, c_in, c_out, km._ordered is not None)):
         order, table, mask = _ordered(mgr, km)
         return _conv_apply(mgr, x, w, 0, 0, table, mask, km.ld, km.n_out, km.K, c_in, c_out, order)
     return _conv_apply(mgr, x, w, 0, 0, km.nbr, _fwd_mask(mgr, km), km.ld, km.n_out, km.K, c_in, c_out)
@@ -294,7 +330,11 @@ def _resolve_out_key(mgr, in_key, out_key, kernel_size, kernel_stride, kernel_di
         out_ts = [t // s for t, s in zip(in_map.tensor_stride, kernel_stride)]
         scale = [d * t for d, t in zip(kernel_dilation, out_ts)]
         offs = region_offsets(kernel_size, scale, region_type, offset)
-        k = mgr._stride_region(in_key, offs, out_ts, expand)
+        k = mgr._octree_children(in_key, offs, out_ts) if expand else None
+        if k is not None:
+            _children_kernel_map(mgr, in_key, k, kernel_size, kernel_stride, kernel_dilation, region_type, offset)
+        else:
+            k = mgr._stride_region(in_key, offs, out_ts, expand)
     out_key.set_key(*k.get_key())
 
 

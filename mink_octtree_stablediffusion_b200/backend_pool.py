@@ -43,8 +43,9 @@ def PruningForwardGPU(in_feat, keep, in_key, out_key, mgr):
                                       _ptr(out), _stream()))
     if not out_key.is_key_set():
         sid = in_key.get_key()[1]
-        key, _, _ = mgr._new_map_from_coords(coords, m.tensor_stride, sid + "p" if sid else "p")
+        key, _, _ = mgr._new_map_from_coords(coords, m.tensor_stride, sid + "p" if sid else "p", unique=True)
         out_key.set_key(*key.get_key())
+        mgr._get(out_key).on_grid = m.on_grid
     else:
         _require(mgr.size(out_key) == n_kept, "pruning: preset out_key has a different size")
     if not hasattr(mgr, "_prune_rows"):

@@ -391,6 +391,156 @@ static int rows_copy(const void *src, const int32_t *idx, int64_t n_idx,
   return MK_OK;
 }
 
+
+// ---------------------------------------------------------------------------
+// mk_map_insert2: the same result as mk_map_insert in three launches (four with the
+// inverse map) and no memset:
+//   k_table_clear2   table + scan state + status words
+//   k_insert         (as above)
+//   k_dedup_compact  first-occurrence flags, ONE-pass ordered compaction (decoupled look-back
+//                    over 2048-row blocks handed out by a ticket), coordinates / unique index
+//                    out, compact ids written into the table, unique count by the last block
+//   k_inverse_map    inverse_map[i] = id in the slot of row i (only when asked for)
+// Why the slot update is race-free inside the compaction pass: a slot holds the first row f
+// of its coordinate until f's own thread replaces it by f's compact id, and id(f) <= f < i
+// for every other row i of that coordinate, so "slot == i" stays false for them whichever
+// value they read.  With MK_INSERT_UNIQUE the caller guarantees distinct rows (children of
+// distinct octree parents, pruned rows of a map): ids are the row numbers, no dedup pass.
+constexpr unsigned kLbAggregate = 1u << 30, kLbPrefix = 2u << 30, kLbMask = (1u << 30) - 1u;
+
+__global__ void k_table_clear2(uint4 *__restrict__ table, int64_t n16, unsigned *__restrict__ state, int64_t nstate,
+                               int32_t *__restrict__ status, int64_t *__restrict__ n_unique) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (int64_t i = t0; i < n16; i += stride)
+    table[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+  for (int64_t i = t0; i < nstate; i += stride) state[i] = 0u;
+  if (t0 == 0) { *status = 0; *n_unique = 0; }
+}
+
+// rows distinct by contract: slot row = row number
+__global__ void k_insert_unique(const int32_t *__restrict__ coords, int64_t n, int ncols, Bucket *__restrict__ table,
+                                uint32_t mask, int32_t *__restrict__ status) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  load_coord(coords, i, ncols, b, x, y, z);
+  if (!coord_in_range(b, x, y, z)) { atomicMax(status, MK_ERANGE); return; }
+  const unsigned long long key = run_key(b, x, y, z);
+  uint32_t h = bucket_home(key, mask);
+  for (uint32_t probes = 0; probes <= mask; ++probes) {
+    unsigned long long old = *(volatile unsigned long long *)&table[h].key;
+    if (old == kEmptyKey) old = atomicCAS(&table[h].key, kEmptyKey, key);
+    if (old == kEmptyKey || old == key) {
+      table[h].row[x & 3] = (uint32_t)i;
+      return;
+    }
+    h = (h + 1) & mask;
+  }
+  atomicMax(status, MK_EFULL);
+}
+
+template <typename IdxT>
+__global__ void __launch_bounds__(kScanThreads)
+k_dedup_compact(const int32_t *__restrict__ coords, int ncols, Bucket *__restrict__ table,
+                const int32_t *__restrict__ slot_of_row, int64_t n, unsigned *__restrict__ state /* [0] = ticket */,
+                IdxT *__restrict__ unique_index, int32_t *__restrict__ coords_out, int64_t *__restrict__ n_unique) {
+  __shared__ int warp_cnt[kScanItems][kScanThreads / 32];
+  __shared__ unsigned s_block, s_prefix;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_block = atomicAdd(&state[0], 1u);      // blocks enter the scan in ticket order
+  __syncthreads();
+  const unsigned blk = s_block;
+  unsigned *lb = state + 1;
+  const int64_t base = (int64_t)blk * kScanTile;
+  bool first[kScanItems];
+  unsigned bal[kScanItems];
+#pragma unroll
+  for (int r = 0; r < kScanItems; ++r) {
+    const int64_t i = base + r * kScanThreads + threadIdx.x;
+    first[r] = false;
+    if (i < n) {
+      const int32_t s = slot_of_row[i];
+      first[r] = s >= 0 && *(volatile uint32_t *)slot_row(table, s) == (uint32_t)i;
+    }
+    bal[r] = __ballot_sync(0xffffffffu, first[r]);
+    if (lane == 0) warp_cnt[r][warp] = __popc(bal[r]);
+  }
+  __syncthreads();
+  // block aggregate -> published; exclusive prefix by looking back over the predecessors
+  if (warp == 0) {
+    unsigned tot = 0;
+    for (int e = lane; e < kScanItems * (kScanThreads / 32); e += 32) tot += (unsigned)(&warp_cnt[0][0])[e];
+    tot = __reduce_add_sync(0xffffffffu, tot);
+    if (lane == 0) {
+      __threadfence();
+      atomicExch(&lb[blk], (blk == 0 ? kLbPrefix : kLbAggregate) | tot);
+    }
+    unsigned excl = 0;
+    int64_t look = (int64_t)blk - 1;
+    while (look >= 0) {
+      const int64_t j = look - lane;
+      unsigned v = kLbPrefix;                       // lanes before block 0: a zero prefix
+      if (j >= 0) {
+        do { v = *(volatile unsigned *)&lb[j]; } while ((v & ~kLbMask) == 0u);
+      }
+      const unsigned is_prefix = __ballot_sync(0xffffffffu, (v & ~kLbMask) == kLbPrefix);
+      const int stop = is_prefix ? __ffs((int)is_prefix) - 1 : 32;    // nearest predecessor holding a prefix
+      const unsigned contrib = lane <= stop ? (v & kLbMask) : 0u;
+      excl += __reduce_add_sync(0xffffffffu, contrib);
+      if (is_prefix) break;
+      look -= 32;
+    }
+    if (lane == 0) {
+      if (blk != 0) { __threadfence(); atomicExch(&lb[blk], kLbPrefix | (excl + tot)); }
+      s_prefix = excl;
+      if ((int64_t)(blk + 1) * kScanTile >= n) *n_unique = (int64_t)(excl + tot);
+    }
+  }
+  __syncthreads();
+  unsigned running = s_prefix;
+#pragma unroll
+  for (int r = 0; r < kScanItems; ++r) {
+    int woff = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+      const int c = warp_cnt[r][w];
+      if (w < warp) woff += c;
+      tot += c;
+    }
+    if (first[r]) {
+      const int64_t i = base + r * kScanThreads + threadIdx.x;
+      const unsigned id = running + (unsigned)woff + (unsigned)__popc(bal[r] & ((1u << lane) - 1u));
+      if (unique_index) unique_index[id] = (IdxT)i;
+      if (coords_out) {
+        int b, x, y, z;
+        load_coord(coords, i, ncols, b, x, y, z);
+        store_coord(coords_out, id, ncols, b, x, y, z);
+      }
+      *slot_row(table, slot_of_row[i]) = id;
+    }
+    running += (unsigned)tot;
+  }
+}
+
+template <typename IdxT>
+__global__ void k_inverse_map(const Bucket *__restrict__ table, const int32_t *__restrict__ slot_of_row, int64_t n,
+                              IdxT *__restrict__ inverse_map) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t s = slot_of_row[i];
+  inverse_map[i] = s >= 0 ? (IdxT)table[s >> 2].row[s & 3] : (IdxT)-1;
+}
+
+__global__ void k_set_count(int64_t *p, int64_t v) { *p = v; }
+
+template <typename IdxT>
+__global__ void k_iota(IdxT *__restrict__ a, IdxT *__restrict__ b, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (a) a[i] = (IdxT)i;
+  if (b) b[i] = (IdxT)i;
+}
 }  // namespace mk
 
 using namespace mk;
@@ -465,6 +615,68 @@ int mk_map_insert(const int32_t *coords, int64_t n, int ncols, void *table,
   k_finalize<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(
       (Bucket *)table, slot_of_row, first_of_row, newid, n, inverse_map);
   MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+int64_t mk_insert2_workspace_bytes(int64_t n) {
+  const int64_t nblk = ceil_div(n > 0 ? n : 1, kScanTile);
+  return align256(n * 4) + align256((nblk + 2) * 4) + 256;
+}
+
+int mk_map_insert2(const int32_t *coords, int64_t n, int ncols, void *table, int64_t capacity, int flags,
+                   void *unique_index, void *inverse_map, int32_t *coords_out, void *workspace,
+                   int64_t *n_unique_dev, int32_t *status_dev, void *stream) {
+  MK_CHECK_ARG(ncols >= 2 && ncols <= 4, "ncols must be in [2,4] (D <= 3)");
+  MK_CHECK_ARG(n >= 0 && n < (int64_t)(1 << 30), "row count out of range");
+  MK_CHECK_ARG(capacity >= 4 * n && capacity >= 1024 && (capacity & (capacity - 1)) == 0 &&
+                   capacity <= ((int64_t)1 << 29),
+               "capacity must be a power of two in [max(4n, 1024), 2^29]");
+  MK_CHECK_ARG(table && n_unique_dev && status_dev && (workspace || n == 0), "null pointer");
+  MK_CHECK_ARG((uintptr_t)table % 32 == 0, "table must be 32-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool unique = (flags & MK_INSERT_UNIQUE) != 0, idx64 = (flags & MK_INSERT_INT64_MAPS) != 0;
+  char *ws = (char *)workspace;
+  int32_t *slot_of_row = (int32_t *)ws;
+  const int64_t nblk = ceil_div(n > 0 ? n : 1, kScanTile);
+  unsigned *state = n > 0 ? (unsigned *)(ws + align256(n * 4)) : nullptr;
+  {
+    const int threads = 256;
+    const int blocks = (int)std::min<int64_t>(ceil_div(capacity, threads), (int64_t)num_sms() * 16);
+    k_table_clear2<<<blocks, threads, 0, st>>>((uint4 *)table, capacity, state, n > 0 ? nblk + 1 : 0, status_dev,
+                                               n_unique_dev);
+    MK_LAUNCH_CHECK();
+  }
+  if (n == 0) return MK_OK;
+  const uint32_t mask = (uint32_t)(capacity / 2 - 1);
+  const unsigned g256 = (unsigned)ceil_div(n, 256);
+  if (unique) {
+    k_insert_unique<<<g256, 256, 0, st>>>(coords, n, ncols, (Bucket *)table, mask, status_dev);
+    MK_LAUNCH_CHECK();
+    if (coords_out && coords_out != coords)
+      MK_CUDA(cudaMemcpyAsync(coords_out, coords, (size_t)n * ncols * 4, cudaMemcpyDeviceToDevice, st));
+    if (unique_index || inverse_map) {
+      if (idx64) k_iota<int64_t><<<g256, 256, 0, st>>>((int64_t *)unique_index, (int64_t *)inverse_map, n);
+      else k_iota<int32_t><<<g256, 256, 0, st>>>((int32_t *)unique_index, (int32_t *)inverse_map, n);
+      MK_LAUNCH_CHECK();
+    }
+    k_set_count<<<1, 1, 0, st>>>(n_unique_dev, n);
+    MK_LAUNCH_CHECK();
+    return MK_OK;
+  }
+  k_insert<<<g256, 256, 0, st>>>(coords, n, ncols, (Bucket *)table, mask, slot_of_row, status_dev);
+  MK_LAUNCH_CHECK();
+  if (idx64)
+    k_dedup_compact<int64_t><<<(unsigned)nblk, kScanThreads, 0, st>>>(coords, ncols, (Bucket *)table, slot_of_row, n, state,
+                                                                      (int64_t *)unique_index, coords_out, n_unique_dev);
+  else
+    k_dedup_compact<int32_t><<<(unsigned)nblk, kScanThreads, 0, st>>>(coords, ncols, (Bucket *)table, slot_of_row, n, state,
+                                                                      (int32_t *)unique_index, coords_out, n_unique_dev);
+  MK_LAUNCH_CHECK();
+  if (inverse_map) {
+    if (idx64) k_inverse_map<int64_t><<<g256, 256, 0, st>>>((const Bucket *)table, slot_of_row, n, (int64_t *)inverse_map);
+    else k_inverse_map<int32_t><<<g256, 256, 0, st>>>((const Bucket *)table, slot_of_row, n, (int32_t *)inverse_map);
+    MK_LAUNCH_CHECK();
+  }
   return MK_OK;
 }
 

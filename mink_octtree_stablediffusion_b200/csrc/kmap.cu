@@ -478,4 +478,50 @@ int mk_kmap_pairs(const int32_t *nbr, int64_t n_out, int64_t ld, int K,
   return MK_OK;
 }
 
+
+// ---------------------------------------------------------------------------
+// Octree split (generative transposed convolution with kernel == stride, extern.hpp:151-165
+// with expand_coordinates; modules/vae_block.py:279-296): the K children of a parent are new
+// by construction and the child at row i*K + k hangs under offset k of parent i, so the
+// kernel map needs no probe: every form the convolution kernels read is written directly.
+//   nbr         [K, ld_out]  nbr[k][o] = o / K if o % K == k else -1        (fine row -> parent)
+//   inv         [K, ld_in]   inv[k][i] = i * K + k                          (parent -> child: dense)
+//   order       [n_out]      tile order: column s = child (s % n_in) under offset s / n_in,
+//   nbr_ordered [K, ld_out]  so a 128-row tile holds ONE offset (two at a segment boundary)
+//                            instead of all K at 1/K fill
+__global__ void k_kmap_children(int64_t n_in, int K, int64_t ld_out, int64_t ld_in, int32_t *__restrict__ nbr,
+                                int32_t *__restrict__ inv, int32_t *__restrict__ order,
+                                int32_t *__restrict__ nbr_ordered) {
+  const int64_t n_out = n_in * K;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (int64_t e = t0; e < (int64_t)K * ld_out; e += stride) {
+    const int k = (int)(e / ld_out);
+    const int64_t o = e - (int64_t)k * ld_out;
+    if (nbr) nbr[e] = (o < n_out && (int)(o % K) == k) ? (int32_t)(o / K) : -1;
+    if (nbr_ordered) nbr_ordered[e] = (o < n_out && (int)(o / n_in) == k) ? (int32_t)(o % n_in) : -1;
+  }
+  if (inv)
+    for (int64_t e = t0; e < (int64_t)K * ld_in; e += stride) {
+      const int k = (int)(e / ld_in);
+      const int64_t i = e - (int64_t)k * ld_in;
+      inv[e] = i < n_in ? (int32_t)(i * K + k) : -1;
+    }
+  if (order)
+    for (int64_t s = t0; s < n_out; s += stride) order[s] = (int32_t)((s % n_in) * K + s / n_in);
+}
+
+int mk_kmap_children(int64_t n_in, int K, int64_t ld_out, int64_t ld_in, int32_t *nbr, int32_t *inv, int32_t *order,
+                     int32_t *nbr_ordered, void *stream) {
+  MK_CHECK_ARG(n_in >= 0 && K >= 1 && K <= 128, "bad sizes");
+  MK_CHECK_ARG(n_in * K < (int64_t)0x7fffffff, "too many children");
+  MK_CHECK_ARG(ld_out >= n_in * K && ld_in >= n_in, "leading dimensions too small");
+  const int64_t total = std::max((int64_t)K * ld_out, (int64_t)K * ld_in);
+  if (total == 0) return MK_OK;
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 16);
+  k_kmap_children<<<grid, 256, 0, (cudaStream_t)stream>>>(n_in, K, ld_out, ld_in, nbr, inv, order, nbr_ordered);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
 }  // extern "C"

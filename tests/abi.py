@@ -41,6 +41,28 @@ def insert(coords_np):
                 inverse=inv[:n].cpu().numpy(), coords=cout[:nu].cpu().numpy(), coords_dev=cout[:nu].contiguous())
 
 
+def insert2(coords_np, unique=False, int64_maps=False):
+    """mk_map_insert2 (fused dedup / compaction pass)."""
+    lib = _lib.load()
+    c = torch.from_numpy(np.ascontiguousarray(coords_np)).cuda()
+    n, ncols = c.shape
+    cap = int(lib.mk_hash_capacity(n))
+    table = torch.empty(cap * 16, dtype=torch.uint8, device="cuda")
+    ws = torch.empty(int(lib.mk_insert2_workspace_bytes(n)), dtype=torch.uint8, device="cuda")
+    dt = torch.int64 if int64_maps else torch.int32
+    uniq = torch.full((max(n, 1),), -7, dtype=dt, device="cuda")
+    inv = torch.full((max(n, 1),), -7, dtype=dt, device="cuda")
+    cout = torch.empty((max(n, 1), ncols), dtype=torch.int32, device="cuda")
+    meta = torch.full((2,), -3, dtype=torch.int64, device="cuda")
+    flags = (1 if unique else 0) | (2 if int64_maps else 0)
+    _lib.check(lib.mk_map_insert2(P(c), n, ncols, P(table), cap, flags, P(uniq), P(inv), P(cout), P(ws),
+                                  C.c_void_p(meta.data_ptr()), C.c_void_p(meta.data_ptr() + 8), S()))
+    h = meta.cpu()
+    nu, status = int(h[0]), int(h[1]) & 0xFFFFFFFF
+    return dict(n_unique=nu, status=status, table=table, cap=cap, unique_index=uniq[:nu].cpu().numpy(),
+                inverse=inv[:n].cpu().numpy(), coords=cout[:nu].cpu().numpy(), coords_dev=cout[:nu].contiguous())
+
+
 def lookup(table, cap, query_np):
     lib = _lib.load()
     q = torch.from_numpy(np.ascontiguousarray(query_np)).cuda()

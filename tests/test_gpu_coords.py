@@ -156,3 +156,68 @@ def test_kernel_map_empty():
     nbr, ld, counts = abi.kmap_build(torch.from_numpy(c).cuda(), tin["table"], tin["cap"],
                                      O.kernel_offsets([3, 3, 3], [1, 1, 1]))
     assert counts.sum() == 0
+
+
+@pytest.mark.parametrize("n,dup", [(1, 0.0), (2047, 0.3), (2049, 0.0), (300_000, 0.5), (1_000_003, 0.05), (70_000, 0.999)])
+def test_insert2_matches_insert_and_oracle(n, dup):
+    """mk_map_insert2 (one-pass dedup / ordered compaction, decoupled look-back) == mk_map_insert == oracle."""
+    c = random_cloud(n, 40 if dup > 0.9 else 300, 3, seed=n, dup_frac=dup)
+    a = abi.insert(c)
+    for i64 in (False, True):
+        b = abi.insert2(c, int64_maps=i64)
+        assert b["status"] == 0 and b["n_unique"] == a["n_unique"]
+        assert np.array_equal(b["unique_index"], a["unique_index"])
+        assert np.array_equal(b["inverse"], a["inverse"])
+        assert np.array_equal(b["coords"], a["coords"])
+        q = c[:: max(1, n // 5000)]
+        assert np.array_equal(abi.lookup(b["table"], b["cap"], q), abi.lookup(a["table"], a["cap"], q))
+    u, ui, inv = O.insert_and_map(c)
+    assert np.array_equal(b["coords"], u) and np.array_equal(b["unique_index"], ui) and np.array_equal(b["inverse"], inv)
+    # rows known to be distinct: no dedup pass, ids = row numbers
+    d = abi.insert2(u, unique=True)
+    assert d["n_unique"] == len(u) and np.array_equal(d["coords"], u)
+    assert np.array_equal(d["unique_index"], np.arange(len(u))) and np.array_equal(d["inverse"], np.arange(len(u)))
+    assert np.array_equal(abi.lookup(d["table"], d["cap"], u), np.arange(len(u)))
+
+
+def test_octree_children_map_closed_form_equals_probed_map():
+    """mk_kmap_children (no probes) == the probed transposed kernel map of the same octree split, and the
+    ME path that uses it gives the oracle's generative coordinates and features."""
+    import MinkowskiEngine as ME
+    from mink_octtree_stablediffusion_b200 import _lib
+    lib = _lib.load()
+    c = O.sphere_surface(40, 0, 0)
+    coarse = O.stride_coords(np.concatenate([c, O.sphere_surface(25, 1, 1)]), [4, 4, 4])
+    offs = O.kernel_offsets([2, 2, 2], [2, 2, 2])
+    fine = (coarse[:, None, :].astype(np.int64) + np.concatenate([np.zeros((8, 1), np.int64), offs], 1)[None]).reshape(-1, 4)
+    tin = abi.insert(coarse)
+    nbr_p, ld, _ = abi.kmap_build(torch.from_numpy(fine.astype(np.int32)).cuda(), tin["table"], tin["cap"], -offs)
+    n_in, n_out = len(coarse), len(fine)
+    ld_in = max(128, (n_in + 127) // 128 * 128)
+    nbr = torch.empty((8, ld), dtype=torch.int32, device="cuda")
+    inv = torch.empty((8, ld_in), dtype=torch.int32, device="cuda")
+    order = torch.empty(n_out, dtype=torch.int32, device="cuda")
+    nbr_o = torch.empty((8, ld), dtype=torch.int32, device="cuda")
+    _lib.check(lib.mk_kmap_children(n_in, 8, ld, ld_in, abi.P(nbr), abi.P(inv), abi.P(order), abi.P(nbr_o), abi.S()))
+    assert torch.equal(nbr, nbr_p)
+    inv_p, _ = abi.kmap_invert(nbr_p, n_out, ld, 8, n_in)
+    assert torch.equal(inv, inv_p)
+    o = order.long()
+    assert torch.equal(torch.sort(o)[0], torch.arange(n_out, device="cuda"))
+    assert torch.equal(nbr_o[:, :n_out], nbr[:, :n_out][:, o]) and bool((nbr_o[:, n_out:] == -1).all())
+    # through the ME API: generative transpose k2 s2 (bf16: tile-ordered closed form; fp32: plain)
+    ref_km = O.kernel_map_transpose(coarse, fine.astype(np.int32), offs)
+    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 1e-2)):
+        torch.manual_seed(0)
+        up = ME.MinkowskiGenerativeConvolutionTranspose(32, 16, kernel_size=2, stride=2, dimension=3).to(dtype).cuda()
+        x = torch.randn(n_in, 32).to(dtype).cuda().requires_grad_(True)
+        st = ME.SparseTensor(x, torch.from_numpy(coarse).cuda(), tensor_stride=4)
+        out = up(st)
+        assert out.tensor_stride == [2, 2, 2] and np.array_equal(out.C.cpu().numpy(), fine)
+        dy = torch.randn(n_out, 16).to(dtype).cuda()
+        out.F.backward(dy)
+        xr, wr, dyr = (t.detach().double().cpu().numpy() for t in (x, up.kernel, dy))
+        y_ref = O.conv_forward(xr, wr, ref_km, n_out)
+        gi_ref, gw_ref = O.conv_backward(xr, dyr, wr, ref_km)
+        rel = lambda a, b: float(np.abs(a.detach().double().cpu().numpy() - b).max() / np.abs(b).max())  # noqa: E731
+        assert rel(out.F, y_ref) <= tol and rel(x.grad, gi_ref) <= tol and rel(up.kernel.grad, gw_ref) <= tol
