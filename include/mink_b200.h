@@ -294,6 +294,10 @@ int mk_conv_wgrad_ex(int dtype, const void *x, const void *dy,
                      int64_t n_in, int K, int c_in, int c_out, void *dw,
                      int dw_f32, void *workspace, int64_t workspace_bytes,
                      void *stream);
+/* 1 if the row-permuted forms (out_rows / dy_rows on a tile-ordered table) are served for this
+ * dtype and shape: the tensor-core kernels, or for MK_F32 beyond the split path's accumulation
+ * limit the tuned FFMA kernels (conv_simt2.cu; c_in and c_out multiples of 4). */
+int mk_conv_rows_eligible(int dtype, int64_t n_rows, int K, int c_in, int c_out);
 /* which implementation the last mk_conv_* call on this thread used:
  * 0 = SIMT tiled kernel, 1 = tcgen05/TMEM kernel */
 int mk_conv_last_path(void);

@@ -62,6 +62,7 @@ PROTOTYPES = {
     "mk_conv_workspace_bytes2": (_i64, [_i, _i64, _i64, _i, _i, _i]),
     "mk_conv_fwd_ex": (_i, [_i, _p, _p, _i, _i, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _p, _p, _i64, _p]),
     "mk_conv_wgrad_ex": (_i, [_i, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p, _i, _p, _i64, _p]),
+    "mk_conv_rows_eligible": (_i, [_i, _i64, _i, _i, _i]),
     "mk_conv_last_path": (_i, []),
     "mk_conv_force_simt": (_i, [_i]),
     "mk_pool_fwd": (_i, [_i, _i, _p, _p, _i64, _i64, _i, _i, _p, _p, _p, _p]),

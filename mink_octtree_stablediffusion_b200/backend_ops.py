@@ -99,7 +99,7 @@ def _want_order(mgr, x, n_rows, K, c_in, c_out, have=False) -> bool:
     threshold below which building it does not pay is moot."""
     on, n_min, _ = _tile_order_cfg()
     return (on and (have or n_rows >= n_min) and x.dtype in (torch.bfloat16, torch.float16, torch.float32)
-            and bool(mgr._lib.mk_conv_tc_eligible(_dtype_code(x), n_rows, K, c_in, c_out)))
+            and bool(mgr._lib.mk_conv_rows_eligible(_dtype_code(x), n_rows, K, c_in, c_out)))
 
 
 def _ordered(mgr, km: _KernelMap):
@@ -288,7 +288,10 @@ def _conv_wgrad(mgr, x, dy, km: _KernelMap, c_in, c_out):
     code = _dtype_code(x)
     ws, nbytes = _workspace(lib, code, km.n_out, x.size(0), km.K, c_in, c_out, x.device)
     table, mask, order = km.nbr, None, None
-    if (km.n_out > 0 and x.size(0) > 0 and _aligned16(x, dy)
+    # (the fp32 FFMA weight-gradient kernel compacts the valid rows of a tile itself and reads dy rows
+    # in place: the plain table is the faster form for it; the tensor-core kernel wants the ordered one)
+    tc = bool(lib.mk_conv_tc_eligible(code, km.n_out, km.K, c_in, c_out))
+    if (km.n_out > 0 and x.size(0) > 0 and _aligned16(x, dy) and tc
             and _want_order(mgr, x, km.n_out, km.K, c_in, c_out, km._ordered is not None)):
         # the ordered table pairs column s with dy row order[s]; the kernel reads dy through it
         order, table, mask = _ordered(mgr, km)

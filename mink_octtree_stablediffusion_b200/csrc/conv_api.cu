@@ -52,6 +52,16 @@ int conv_wgrad_pad16(int dtype, const void *x, const void *dy, const int32_t *dy
                      const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
                      void *dw, int dw_f32, void *workspace, cudaStream_t st);
 
+// conv_simt2.cu: tuned fp32 FFMA kernels (c_in, c_out multiples of 4)
+bool conv_f32_simt2_eligible(int c_in, int c_out, int K);
+int64_t conv_f32_simt2_workspace(int K, int c_in, int c_out);
+int conv_fwd_f32_simt2(const float *x, const float *w, int transpose_w, int kflip, const int32_t *nbr,
+                       const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
+                       float *y, const int32_t *out_rows, void *workspace, cudaStream_t st);
+int conv_wgrad_f32_simt2(const float *x, const float *dy, const int32_t *dy_rows, const int32_t *nbr,
+                         const uint32_t *tile_mask, int64_t ld, int64_t n_out, int K, int c_in, int c_out, float *dw,
+                         cudaStream_t st);
+
 static thread_local int g_last_path = 0;
 static int g_force_simt = 0;
 }  // namespace mk
@@ -106,8 +116,15 @@ int mk_conv_tc_eligible(int dtype, int64_t n_rows, int K, int c_in,
              : 0;
 }
 
+int mk_conv_rows_eligible(int dtype, int64_t n_rows, int K, int c_in, int c_out) {
+  if (mk_conv_tc_eligible(dtype, n_rows, K, c_in, c_out)) return 1;
+  return (!g_force_simt && n_rows > 0 && dtype == MK_F32 && conv_f32_simt2_eligible(c_in, c_out, K)) ? 1 : 0;
+}
+
 int64_t mk_conv_workspace_bytes2(int dtype, int64_t n_out, int64_t n_in, int K, int c_in, int c_out) {
   int64_t b = mk_conv_workspace_bytes(dtype, n_out, K, c_in, c_out);
+  if (dtype == MK_F32 && conv_f32_simt2_eligible(c_in, c_out, K))
+    b = std::max<int64_t>(b, conv_f32_simt2_workspace(K, c_in, c_out));
   if (dtype == MK_F32 && n_out > 0 && n_in > 0) {
     if (conv_fwd_f32_eligible(n_out, K, c_in, c_out))
       b = std::max<int64_t>(b, conv_fwd_f32_workspace(n_out, n_in, K, c_in, c_out));
@@ -174,9 +191,17 @@ int mk_conv_fwd_ex(int dtype, const void *x, const void *w, int transpose_w,
     return conv_fwd_f32((const float *)x, (const float *)w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K,
                         c_in, c_out, (float *)y, out_rows, workspace, st);
   }
+  // fp32 beyond the split path's accumulation limit: the tuned FFMA kernel (also honours out_rows)
+  if (!g_force_simt && dtype == MK_F32 && n_in > 0 && conv_f32_simt2_eligible(c_in, c_out, K) &&
+      (((uintptr_t)x | (uintptr_t)y | (uintptr_t)w) & 15) == 0 &&
+      (!transpose_w || (workspace && workspace_bytes >= conv_f32_simt2_workspace(K, c_in, c_out)))) {
+    g_last_path = 0;
+    return conv_fwd_f32_simt2((const float *)x, (const float *)w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K,
+                              c_in, c_out, (float *)y, out_rows, workspace, st);
+  }
   if (out_rows) {
-    set_error("mk_conv_fwd_rows: an output-row permutation is only served by "
-              "the tensor-core path (ask mk_conv_tc_eligible first)");
+    set_error("mk_conv_fwd_rows: an output-row permutation is not served for this dtype / shape "
+              "(ask mk_conv_rows_eligible first)");
     return MK_EUNSUPPORTED;
   }
   g_last_path = 0;
@@ -219,9 +244,15 @@ int mk_conv_wgrad_ex(int dtype, const void *x, const void *dy,
     return conv_wgrad_f32((const float *)x, (const float *)dy, dy_rows, nbr, tile_mask, ld, n_out, n_in, K, c_in,
                           c_out, (float *)dw, workspace, st);
   }
+  if (!g_force_simt && dtype == MK_F32 && n_in > 0 && n_out > 0 && conv_f32_simt2_eligible(c_in, c_out, K) &&
+      (((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dw) & 15) == 0) {
+    g_last_path = 0;
+    return conv_wgrad_f32_simt2((const float *)x, (const float *)dy, dy_rows, nbr, tile_mask, ld, n_out, K, c_in, c_out,
+                                (float *)dw, st);
+  }
   if (dy_rows) {
-    set_error("mk_conv_wgrad_rows: dy_rows is served by the tensor-core path "
-              "only (eligible shape, 16-byte aligned pointers)");
+    set_error("mk_conv_wgrad_rows: dy_rows is not served for this dtype / shape "
+              "(ask mk_conv_rows_eligible first)");
     return MK_EUNSUPPORTED;
   }
   g_last_path = 0;

@@ -368,6 +368,17 @@ def test_tile_ordered_table(R, order, with_coords):
         abi.conv_fwd_rows(x.double(), w.double(), nbr_t, ld, n, perm)
     with pytest.raises(RuntimeError):
         abi.conv_wgrad(x.double(), dy.double(), nbr_t, ld, n, 27, dy_rows=perm)
+    # fp32 beyond the split path's accumulation limit: the tuned FFMA kernels honour the permutations too
+    xf, wf, dyf = x.float(), w.float(), dy.float()
+    assert not abi.tc_eligible(torch.float32, n, 27, 64, 64)
+    s0 = abi.conv_fwd(xf, wf, nbr, ld, n)
+    s1 = abi.conv_fwd_rows(xf, wf, nbr_t, ld, n, perm, mask=abi.tile_mask(nbr_t, n, ld, 27))
+    assert abi.last_path() == 0 and float((s0 - s1).abs().max() / s0.abs().max()) <= 1e-6
+    s2 = abi.conv_fwd_rows(dyf, wf, nbr_t, ld, n, perm, transpose_w=1, kflip=1)
+    assert float((s2 - abi.conv_fwd(dyf, wf, nbr, ld, n, transpose_w=1, kflip=1)).abs().max() / s2.abs().max()) <= 1e-6
+    v0 = abi.conv_wgrad(xf, dyf, nbr, ld, n, 27)
+    v1 = abi.conv_wgrad(xf, dyf, nbr_t, ld, n, 27, dy_rows=perm)
+    assert float((v0 - v1).abs().max() / v0.abs().max()) <= 1e-5
     # fp32: where the split tensor-core path serves the shape it honours the permutations too
     x32, w32, dy32 = x.float()[:, :32].contiguous(), w.float()[:, :32].contiguous(), dy.float()
     if abi.tc_eligible(torch.float32, n, 27, 32, 64):
