@@ -79,6 +79,42 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
+def bind_rank_to_cpus(local: int, world: int):
+    """Give every rank its own slice of the host cores that are local to its GPU (nvidia-smi topo -m,
+    column 'CPU Affinity'): the e2e leg is bound by the host side (pinned-memory reads, the Python launch
+    thread), and eight ranks floating over the same cores take turns.  Returns a description for the JSON."""
+    info = {"cpus_total": os.cpu_count()}
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+        rows = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout.splitlines()
+        head = next(r for r in rows if "CPU Affinity" in r)
+        cols = [c.strip() for c in head.split("\t")]
+        ci = cols.index("CPU Affinity")
+        aff = {}
+        for r in rows:
+            cells = [c.strip() for c in r.split("\t")]
+            if cells and cells[0].startswith("GPU") and len(cells) > ci:
+                cpus = []
+                for part in cells[ci].split(","):
+                    a, _, b = part.partition("-")
+                    cpus += list(range(int(a), int(b or a) + 1))
+                aff[int(cells[0][3:])] = [c for c in cpus if c in allowed]
+        mine = aff.get(local) or allowed
+        sharing = sorted(g for g, c in aff.items() if c == mine and g < world) or [local]
+        per = max(1, len(mine) // len(sharing))
+        i = sharing.index(local) if local in sharing else 0
+        mine = mine[i * per:(i + 1) * per] or mine
+        os.sched_setaffinity(0, mine)
+        info.update(gpu_cpu_affinity=cells_to_str(aff.get(local, [])), bound_to=cells_to_str(mine))
+    except Exception as e:          # no topology information: leave the affinity alone
+        info["bind_error"] = f"{type(e).__name__}: {e}"
+    return info
+
+
+def cells_to_str(cpus):
+    return f"{cpus[0]}-{cpus[-1]} ({len(cpus)})" if cpus else ""
+
+
 def make_cloud(R: int, seed: int, batch_index: int = 0) -> np.ndarray:
     """G1 sphere-surface generator, int32 [N, 4], batch first."""
     rng = np.random.default_rng(seed)
@@ -159,6 +195,7 @@ def run_engine(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; this engine has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    host_info = bind_rank_to_cpus(local, world) if world > 1 and not args.no_bind else {"cpus_total": os.cpu_count()}
     if world > 1:
         import datetime
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=180))
@@ -189,6 +226,8 @@ def run_engine(args):
     empty_off = torch.empty(0, dtype=torch.int32)
     conv_args = (kg.kernel_size, kg.kernel_stride, kg.kernel_dilation, kg.region_type, empty_off)
 
+    pending = [None, None]      # (work handle, tensor) of the all-reduce in flight
+
     def step_resident(ev=None):
         if ev:
             ev[0].record()
@@ -199,7 +238,13 @@ def run_engine(args):
         if ev:
             ev[2].record()
         if world > 1:
-            dist.all_reduce(gw)                     # weight gradients only
+            # weight gradients only.  Asynchronous: the collective runs on NCCL's stream while
+            # the next step's forward is already on the compute stream; it is waited for one step later
+            # (a training loop consumes the reduced gradient in the optimizer, after the next launch burst)
+            if pending and pending[0] is not None:
+                pending[0].wait()
+            pending[0] = dist.all_reduce(gw, async_op=True)
+            pending[1] = gw
         return out, gi, gw
 
     out, gi, gw = step_resident()
@@ -228,6 +273,8 @@ def run_engine(args):
     t_start.record()
     for i in range(args.steps):
         step_resident(evs[i])
+    if pending[0] is not None:
+        pending[0].wait()                           # the last step's all-reduce belongs to the timed region
     t_end.record()
     sync_all()
     launches = int(lib.mk_launch_count()) - launches0
@@ -323,6 +370,22 @@ def run_engine(args):
             ms1["num_alloc_retries"], ms1["reserved_bytes.all.current"] / 1e9), file=sys.stderr)
     sync_all()
     ms_e2e = e0.elapsed_time(e1)
+    # the ceiling of the e2e leg: nothing but its host-to-device copies, all ranks at once
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(copy_stream):
+        for i in range(3):
+            bufs[i & 1][1].copy_(feats_h, non_blocking=True)
+        copy_stream.synchronize()
+        if world > 1:
+            dist.barrier()
+        h0.record(copy_stream)
+        for i in range(10):
+            bufs[i & 1][0].copy_(coords_h, non_blocking=True)
+            bufs[i & 1][1].copy_(feats_h, non_blocking=True)
+        h1.record(copy_stream)
+    copy_stream.synchronize()
+    ms_h2d = h0.elapsed_time(h1) / 10
+    sync_all()
 
     # ---- integer stages, timed alone (new map each iteration) ----------------
     stage = {}
@@ -476,10 +539,10 @@ def run_engine(args):
                 raise
 
     # ---- reduce over ranks -----------------------------------------------------
-    t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms, ms_h2d], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e, fwd_ms, bwd_ms = t.tolist()
+    ms_total, ms_e2e, fwd_ms, bwd_ms, ms_h2d = t.tolist()
     if rank == 0:
         ms_step = ms_total / args.steps
         value = n * world / (ms_step * 1e-3)
@@ -511,6 +574,9 @@ def run_engine(args):
             "e2e": {"value": e2e_val, "unit": UNIT,
                     "h2d_bytes_per_step": int(coords_h.numel() * 4 + feats_h.numel() * 2),
                     "d2h_bytes_per_step": int(grad_h.numel() * 2 + 4),
+                    "h2d_only_ms_per_step": ms_h2d, "h2d_ceiling_voxels_per_s": n * world / (ms_h2d * 1e-3),
+                    "h2d_gb_per_s_per_rank": (coords_h.numel() * 4 + feats_h.numel() * 2) / (ms_h2d * 1e-3) / 1e9,
+                    "host": host_info,
                     "path": "pinned host coords+features -> ME.SparseTensor (hash insert) -> MinkowskiConvolution "
                             "(kernel-map build + fwd) -> backward -> grad_kernel + checksum to host",
                     "pipeline": "two buffer sets: step i+1's H2D copy (copy stream) and launch overlap step i's kernels "
@@ -670,6 +736,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vae", action="store_true", help="skip the VAE steps/s leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the wide-layer rooflines and the cfg1 leg")
+    ap.add_argument("--no-bind", action="store_true", help="do not bind the ranks to their GPUs' host cores")
     ap.add_argument("--no-vae-profile", action="store_true")
     ap.add_argument("--vae-steps", type=int, default=10)
     ap.add_argument("--vae-warmup", type=int, default=3)
