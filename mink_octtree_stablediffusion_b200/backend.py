@@ -132,7 +132,14 @@ def _ptr(t: Optional[torch.Tensor]):
     return ctypes.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else None
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream() -> ctypes.c_void_p:
+    """PyTorch's current CUDA stream of the current device (every kernel is launched there).  The raw
+    query is ~10x cheaper than building a torch.cuda.Stream object, and this runs once per launch."""
+    if _raw_stream is not None:
+        return ctypes.c_void_p(_raw_stream(torch.cuda.current_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

@@ -254,8 +254,16 @@ def _check_conv(in_feat, kernel, in_key, mgr, c_in_axis=1):
 CONV_LOG = None      # development aid: set to a list to record (kind, n_out, n_in, K, c_in, c_out, dtype) per launch
 
 
+_WS_BYTES: Dict[tuple, int] = {}
+
+
 def _workspace(lib, dtype_code, n_out, n_in, K, c_in, c_out, dev):
-    nbytes = int(lib.mk_conv_workspace_bytes2(dtype_code, n_out, n_in, K, c_in, c_out))
+    key = (dtype_code, n_out, n_in, K, c_in, c_out)
+    nbytes = _WS_BYTES.get(key)
+    if nbytes is None:
+        if len(_WS_BYTES) > 4096:
+            _WS_BYTES.clear()
+        nbytes = _WS_BYTES[key] = int(lib.mk_conv_workspace_bytes2(dtype_code, n_out, n_in, K, c_in, c_out))
     return torch.empty(nbytes, dtype=torch.uint8, device=dev), nbytes
 
 

@@ -86,6 +86,9 @@ struct ConvTCParams {
   int b_merged;           // weight ring = A ring (same depth): image s travels with stage s on the stage's barriers
   int c_in, c_out, nchunk, NT, T;
   int a_stages, b_stages, i_slots;
+  int half_cols;          // TMEM columns between the two accumulator halves: 256, or 0 = one accumulator set only
+                          // (wide outputs: twice the tiles per group, i.e. per weight image, instead of an
+                          // epilogue that overlaps the next group)
   int ngroups;
   uint32_t idesc;
 };
@@ -234,6 +237,8 @@ struct GroupQueue {
 //   bits 0-3 tiles present, bits 4-7 tiles whose accumulator already holds data,
 //   bit 8 TMEM half, bits 16-18 K steps
 constexpr uint32_t kTkGroupBegin = 1u << 12, kTkGroupEnd = 1u << 13, kTkEmptyParity = 1u << 14, kTkEnd = 1u << 15;
+// single accumulator set (half_cols == 0): the group must also wait for the epilogue of the PREVIOUS group
+constexpr uint32_t kTkPrevParity = 1u << 9, kTkHasPrev = 1u << 10;
 
 // 16 accumulator columns -> 16 outputs of type TOut (T: 2 x 16-byte stores; float: 4)
 template <typename T, typename TOut>
@@ -340,7 +345,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         const int64_t row = tile * kTileM + warp * 32 + lane;   // table column
         const int64_t orow = (p.out_rows && row < p.n_out) ? (int64_t)__ldg(p.out_rows + row) : row;
         TOut *yrow = (TOut *)p.y + (size_t)orow * p.c_out + (size_t)sp * p.NT;
-        const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * 256 + t * acc_stride);
+        const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * p.half_cols + t * acc_stride);
         for (int c0 = 0; c0 < p.NT; c0 += 16) {
           uint32_t v[16];
           if (touched) {
@@ -447,7 +452,9 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         any2 = __ballot_sync(0xffffffffu, 64 + lane < p.K && lds_u8(sched_s + 64u + (uint32_t)lane) != 0u);
         any3 = __ballot_sync(0xffffffffu, 96 + lane < p.K && lds_u8(sched_s + 96u + (uint32_t)lane) != 0u);
       }
-      const uint32_t tk_group = (it & 1u) << 8 | ((((it >> 1) & 1u) ^ 1u) ? kTkEmptyParity : 0u);
+      uint32_t tk_group = (it & 1u) << 8 | ((((it >> 1) & 1u) ^ 1u) ? kTkEmptyParity : 0u);
+      if (p.half_cols == 0 && it > 0)     // completion ((it-1)>>1)+1 of the other barrier = epilogue of group it-1
+        tk_group |= kTkHasPrev | ((((it - 1u) >> 1) & 1u) ? kTkPrevParity : 0u);
       uint32_t seen = 0, done = 0;                 // tiles already accumulated into / stages of the group so far
 #pragma unroll 1
       for (int j = 0; j < 4; ++j) {
@@ -571,7 +578,10 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         if (tk & kTkEnd) break;
         const uint32_t h = (tk >> 8) & 1u;
         PROF_T0(pm_t0);
-        if (tk & kTkGroupBegin) mbar_wait_shared(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
+        if (tk & kTkGroupBegin) {
+          mbar_wait_shared(&t_empty[h], (tk & kTkEmptyParity) ? 1u : 0u);
+          if (tk & kTkHasPrev) mbar_wait_shared(&t_empty[h ^ 1u], (tk & kTkPrevParity) ? 1u : 0u);
+        }
         PROF_ADD(pm_wt, pm_t0);
         PROF_T0(pm_t0);
         if (!p.b_merged) mbar_wait_shared(&b_full[bs], bph);
@@ -579,7 +589,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         PROF_T0(pm_t0);
         tc_fence_after();
         const uint64_t bd0 = desc0 | (uint64_t)(((b_base + (p.b_merged ? s : bs) * b_bytes) & 0x3FFFFu) >> 4);
-        const uint32_t d0 = tm_base + h * 256u;
+        const uint32_t d0 = tm_base + h * (uint32_t)p.half_cols;
         const uint32_t a0 = a_base + s * stage_bytes;
         if (elect_one()) {
           PROF_DECL(pq_t0 = clock64();)
@@ -689,26 +699,24 @@ static int arm_hang_report() {
 }
 
 struct TCPlan {
-  int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots, b_merged;
+  int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots, b_merged, half_cols;
   size_t smem, bpack_bytes, mask_bytes, range_bytes;
 };
 
 static inline size_t align256s(size_t b) { return (b + 255) & ~(size_t)255; }
 
-static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPlan &pl) {
-  if (dtype != MK_BF16 && dtype != MK_F16) return false;
-  if (c_in < 16 || c_in % 16 || c_out < 16 || c_out % 16 || K < 1 || K > kMaxK || n_out < 1) return false;
+// One candidate: T tiles per group on accumulator halves `half_cols` apart (0 = a single set).
+static bool plan_with(int64_t n_out, int K, int c_in, int c_out, int T, int half_cols, TCPlan &pl) {
   int nsplit = (c_out + 255) / 256;
   while (c_out % (16 * nsplit)) ++nsplit;
   pl.nsplit = nsplit;
   pl.NT = c_out / nsplit;
   pl.nchunk = (c_in + 63) / 64;
-  const int acc_stride = (pl.NT + 31) & ~31;
-  pl.T = std::min(kMaxT, 256 / acc_stride);
+  pl.T = T;
+  pl.half_cols = half_cols;
   pl.b_stages = 2;
   pl.i_slots = 4;
-  // development knobs (tuning sweeps): MK_TC_T / MK_TC_BSTAGES / MK_TC_ISLOTS
-  if (const char *e = getenv("MK_TC_T")) pl.T = std::max(1, std::min(pl.T, atoi(e)));
+  // development knobs (tuning sweeps): MK_TC_BSTAGES / MK_TC_ISLOTS
   if (const char *e = getenv("MK_TC_BSTAGES")) pl.b_stages = std::max(2, std::min(kMaxBStages, atoi(e)));
   // (a multiple of 4: the teams that use an idx slot must be the same every time round the ring)
   if (const char *e = getenv("MK_TC_ISLOTS")) pl.i_slots = std::max(4, std::min(kMaxIdxSlots, atoi(e) & ~3));
@@ -718,6 +726,7 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
                  kSchedCopies * (size_t)((K + 31) & ~31) + 64 + 1024 /*barriers*/;
   const size_t budget = 227 * 1024;
   const size_t stage_bytes = (size_t)pl.T * kTileBytes;
+  if (fixed + 3 * stage_bytes > budget) return false;
   int S = (int)((budget - fixed) / stage_bytes);
   S = std::min(S, 12);   // tickets[] holds 16
   if (S < 3 || S * pl.T <= 4) return false;   // producer teams: consecutive stages of a team must be < S apart
@@ -740,6 +749,30 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   pl.mask_bytes = align256s((size_t)((n_out + kTileM - 1) / kTileM) * pl.W * 4);
   pl.range_bytes = 256;   // group counters, one int per output split
   return true;
+}
+
+static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPlan &pl) {
+  if (dtype != MK_BF16 && dtype != MK_F16) return false;
+  if (c_in < 16 || c_in % 16 || c_out < 16 || c_out % 16 || K < 1 || K > kMaxK || n_out < 1) return false;
+  int nsplit = (c_out + 255) / 256;
+  while (c_out % (16 * nsplit)) ++nsplit;
+  const int acc_stride = (c_out / nsplit + 31) & ~31;
+  int t_two = std::min(kMaxT, 256 / acc_stride);
+  int t_one = std::min(kMaxT, 512 / acc_stride);
+  if (const char *e = getenv("MK_TC_T")) {   // development knob
+    t_two = std::max(1, std::min(t_two, atoi(e)));
+    t_one = std::max(1, std::min(t_one, atoi(e)));
+  }
+  // Wide outputs: with two accumulator sets only 256 / NT tiles share a weight image (ONE at NT = 256: 32 KB
+  // of weights re-read per 16 KB of gathered rows, and the SM ingests ~64 B/clk whatever the source).  One
+  // set of up to 512 columns lets more tiles share an image; the price is that a group's first MMA waits for
+  // the previous group's epilogue (a few thousand cycles per ~100 k cycles of MMA work at these widths).
+  // Taken when it at least doubles the tiles per image and the A ring still holds three stages (128 columns:
+  // four tiles do not fit the ring, and three on one set measured slower than two on each of two sets).
+  if (!getenv("MK_TC_TWO_SETS"))
+    for (int t = t_one; t >= 2 * t_two; --t)
+      if (plan_with(n_out, K, c_in, c_out, t, 0, pl)) return true;
+  return plan_with(n_out, K, c_in, c_out, t_two, 256, pl);
 }
 
 bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) {
@@ -790,6 +823,7 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.ld = ld; p.n_out = n_out; p.n_in = n_in; p.K = K; p.W = pl.W; p.kflip = kflip;
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
   p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots; p.b_merged = pl.b_merged; p.group_counter = group_counter;
+  p.half_cols = pl.half_cols;
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
