@@ -100,6 +100,16 @@ def load(build_if_missing: bool = True) -> C.CDLL:
             raise RuntimeError(f"{LIB_PATH} is missing; run `python -m mink_octtree_stablediffusion_b200.build`")
         from . import build as _build
         _build.build_library()
+    else:
+        # a library older than its sources must not be measured or tested silently: the stamp beside it
+        # names the source digests it was linked from
+        from . import build as _build
+        stale = _build.stale_reason()
+        if stale:
+            if build_if_missing and _build.have_nvcc():
+                _build.build_library()
+            else:
+                raise RuntimeError(f"{LIB_PATH} is stale ({stale}); run `python -m mink_octtree_stablediffusion_b200.build`")
     lib = C.CDLL(str(LIB_PATH))
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)          # AttributeError => symbol missing: fail loudly

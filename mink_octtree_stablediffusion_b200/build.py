@@ -67,6 +67,30 @@ def sources() -> list[Path]:
     return sorted(CSRC.glob("*.cu"))
 
 
+def have_nvcc() -> bool:
+    try:
+        _nvcc()
+        return True
+    except RuntimeError:
+        return False
+
+
+def stale_reason() -> str:
+    """'' if the library's stamp names the digests of the sources (and compiler flags) as they are now.
+    Development builds made with other flags (MK_NVCC_EXTRA=-DMK_TC_PROF ...) are run with
+    MK_ALLOW_STALE_LIB=1."""
+    stamp = LIB_DIR / "libmink_b200.stamp"
+    if not stamp.exists():
+        return "no stamp"
+    have = stamp.read_text()
+    want = ",".join(f"{s.stem}.{_digest(s)}.o" for s in sources())
+    if have == want:
+        return ""
+    if set(n.split(".")[0] for n in have.split(",")) != set(s.stem for s in sources()):
+        return "source files added or removed"
+    return "" if os.environ.get("MK_ALLOW_STALE_LIB") else "sources changed since it was linked"
+
+
 def build_library(force: bool = False, verbose: bool = False) -> Path:
     """Compile every csrc/*.cu for sm_100a and link the shared library."""
     OBJ_DIR.mkdir(parents=True, exist_ok=True)

@@ -30,6 +30,8 @@
 // begin / end) so that the serial MMA warp does no bookkeeping.
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
+#include <type_traits>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -43,7 +45,10 @@ constexpr int kTileBytes = kTileM * 128;   // one gathered tile: 128 rows x 64 1
 // one A stage = the T tiles of a group under one (offset, channel chunk): T * kTileBytes
 constexpr int kGatherTeams = 4;              // stages in flight on the producer side
 constexpr int kGatherWarps = 4 * kGatherTeams;   // 4 warps (32 rows each) per stage
-constexpr int kMmaWarps = 2;   // tile t of a stage belongs to MMA warp t % kMmaWarps.  Every MMA warp waits on
+#ifndef MK_TC_MMA_WARPS
+#define MK_TC_MMA_WARPS 2
+#endif
+constexpr int kMmaWarps = MK_TC_MMA_WARPS;   // tile t of a stage belongs to MMA warp t % kMmaWarps.  Every MMA warp waits on
                                // every stage and commits to its release barrier (count kMmaWarps), so stages are
                                // still released in order: the producers' parity waits stay alias-free
 constexpr int kWarpIdx = 4, kWarpWeights = 5, kWarpMma0 = 6, kWarpGather0 = kWarpMma0 + kMmaWarps;
@@ -86,6 +91,7 @@ struct ConvTCParams {
   int b_merged;           // weight ring = A ring (same depth): image s travels with stage s on the stage's barriers
   int c_in, c_out, nchunk, NT, T;
   int a_stages, b_stages, i_slots;
+  int lean;               // gather warps: the lean loop (T == 4, one channel chunk, one mask word per tile)
   int half_cols;          // TMEM columns between the two accumulator halves: 256, or 0 = one accumulator set only
                           // (wide outputs: twice the tiles per group, i.e. per weight image, instead of an
                           // epilogue that overlaps the next group)
@@ -268,7 +274,7 @@ __device__ __forceinline__ void store16(TOut *dst, const uint32_t (&v)[16]) {
 // bf16 operand pieces in, the fp32 accumulator out as it is)
 template <typename T, bool kFull, typename TOut>
 __global__ void __launch_bounds__(kNumThreadsTC, 1)
-k_conv_tc(const __grid_constant__ ConvTCParams p) {
+k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtensorMap tmap_x) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B-swizzle atoms
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -306,13 +312,14 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
   GroupQueue gq_ctl{gq, gq_full, gq_empty, p.group_counter ? p.group_counter + blockIdx.y : nullptr, p.ngroups};
 
   if (threadIdx.x == 0) {
-    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * 128u + 1u + (p.b_merged ? 1u : 0u)); mbar_init(&a_empty[s], kMmaWarps); }
+    for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * (p.lean == 2 ? 132u : 128u) + 1u + (p.b_merged ? 1u : 0u)); mbar_init(&a_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], (uint32_t)(p.nchunk * p.T) * 4u); }
     for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], kMmaWarps); mbar_init(&t_empty[s], 4); }
     for (int s = 0; s < kGroupQ; ++s) { mbar_init(&gq_full[s], 1); mbar_init(&gq_empty[s], kGroupConsumers); }
     fence_barrier_init();
   }
+  if (warp == kWarpGather0 && lane == 0 && p.lean == 2) tma_prefetch_desc(&tmap_x);
   if (warp == kWarpMma0) tmem_alloc_512(tmem_slot);
   tc_fence_before();
   __syncthreads();
@@ -439,11 +446,120 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
     Ring ir, ar;                                   // idx slot of the row's first tile / current A stage
     uint32_t nst = 0;                              // stages so far
     uint32_t it = 0;                               // groups with work so far
-    PROF_DECL(pg_we = 0, pg_wi = 0, pg_iss = 0, pg_t0 = 0, pg_n = 0;)
+    PROF_DECL(pg_we = 0, pg_wi = 0, pg_iss = 0, pg_t0 = 0, pg_n = 0, pg_start = PROF_NOW(), pg_grp = 0, pg_g0 = PROF_NOW(), pg_abs = 0;)
+    if (kFull && p.lean) {
+      // Lean form of the loop below for the layers the ingest side bounds (Cin = 64, Cout <= 64, K <= 32:
+      // T = 4, one channel chunk, one mask word per tile).  Tile slot t of every stage then belongs to team
+      // t for good, a stage is an offset, and the group's schedule is the four tiles' mask words in
+      // registers: no schedule copy in shared memory, no ballots, no nested loops.  (The general loop
+      // spends ~350 instructions per warp and stage at one instruction per ~6 cycles, of which 8 are
+      // copies: the gather warps' own chain, not the copy rate, set the stage period - DESIGN 4.9.)
+      for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
+        const int64_t tile0 = (int64_t)g * 4;
+        uint32_t mm[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t v = tile0 + j < ntiles ? __ldg(p.mask + tile0 + j) : 0u;
+          if (p.kflip) v = __brev(v) >> (32 - p.K);     // schedule position k <-> table offset K-1-k
+          mm[j] = v;
+        }
+        const uint32_t all = mm[0] | mm[1] | mm[2] | mm[3];
+        PROF_ADD(pg_grp, pg_g0);
+        if (!all) { PROF_T0(pg_g0); continue; }
+        const uint32_t mine = team == 0 ? mm[0] : team == 1 ? mm[1] : team == 2 ? mm[2] : mm[3];
+        uint32_t tk_group = (it & 1u) << 8 | ((((it >> 1) & 1u) ^ 1u) ? kTkEmptyParity : 0u) | (4u << 16);
+        if (p.half_cols == 0 && it > 0)
+          tk_group |= kTkHasPrev | ((((it - 1u) >> 1) & 1u) ? kTkPrevParity : 0u);
+        uint32_t seen = 0;
+#pragma unroll 1
+        for (uint32_t m = all; m; m &= m - 1u, ++nst) {
+          const uint32_t k = (uint32_t)__ffs((int)m) - 1u;
+          const uint32_t a_full_s = b_a_full + ar.stage * 8u;
+          const uint32_t i_full_k = b_i_full + ir.stage * 8u, i_empty_k = b_i_empty + ir.stage * 8u;
+          PROF_T0(pg_t0);
+          mbar_wait_warp_a(b_a_empty + ar.stage * 8u, ar.phase ^ 1u);
+          PROF_ADD(pg_we, pg_t0);
+          if (team == 0 && ticket_lane) {
+            const uint32_t bits = ((mm[0] >> k) & 1u) | ((mm[1] >> k) & 1u) << 1 | ((mm[2] >> k) & 1u) << 2 |
+                                  ((mm[3] >> k) & 1u) << 3;
+            uint32_t tk = tk_group | bits | (seen << 4);
+            if (m == all) tk |= kTkGroupBegin;
+            if (!(m & (m - 1u))) tk |= kTkGroupEnd;
+            sts_u32(tickets_s + ar.stage * 4u, tk);
+            mbar_arrive_a(a_full_s);                 // release: orders the ticket before the phase completes
+            seen |= bits;
+          }
+          PROF_T0(pg_t0);
+          mbar_wait_warp_a(i_full_k, ir.phase);      // (also when the tile is absent: see the general loop)
+          PROF_ADD(pg_wi, pg_t0);
+          if (((mine >> k) & 1u) && p.lean == 2) {
+            // Hybrid ingest.  On a tile-ordered table 71 % of the 4-row groups of a non-empty (tile,
+            // offset) pair are fully valid (96 % of the valid rows), 6 % partly, 23 % empty
+            // (scripts/group_stats.py).  Full groups go through TMA tile::gather4 - one instruction of
+            // one lane per 512 bytes, written by the async proxy with the map's 128-byte swizzle, bytes
+            // counted on the stage's barrier - and only the rest through LDGSTS with zero fill (one warp
+            // instruction per group): the LSU path, which drains a 16 KB tile in ~400 cycles, carries 29 %
+            // of the groups.  gather4 alone is unusable here: a missing row costs it ~10 cycles (4.5).
+            PROF_T0(pg_t0);
+            const uint32_t idx_w = smem_u32(idx_ring) + ir.stage * (4u * kTileM * 4u) + team * (kTileM * 4u) +
+                                   (uint32_t)q * 128u;                    // this warp's 32 table entries
+            int4 gi = make_int4(-1, -1, -1, -1);
+            if (lane < 8) gi = lds_v4(idx_w + (uint32_t)lane * 16u);       // lane j < 8: rows 4j .. 4j+3
+            const bool fullg = (gi.x | gi.y | gi.z | gi.w) >= 0;
+            const uint32_t fm = __ballot_sync(0xffffffffu, fullg);
+            const uint32_t tile_s = smem_u32(a_ring) + ar.stage * (4u * kTileBytes) + team * kTileBytes +
+                                    (uint32_t)q * 4096u;
+            if (lane == 0) mbar_arrive_expect_tx_a(a_full_s, 512u * (uint32_t)__popc(fm));
+            if (fullg) tma_gather4_a(tile_s + (uint32_t)lane * 512u, &tmap_x, 0, gi, a_full_s);
+            // lane (r4, c16) moves chunk c16 of row 4j + r4: bits 4-6 of the address = c16 ^ ((4j + r4) & 7)
+            const uint32_t r4 = (uint32_t)lane >> 3;
+            const uint32_t dst_l = tile_s + r4 * 128u + (((uint32_t)c16 ^ r4) << 4);
+#pragma unroll 1
+            for (uint32_t rest = ~fm & 0xFFu; rest; rest &= rest - 1u) {
+              const uint32_t j = (uint32_t)__ffs((int)rest) - 1u;
+              const int32_t r = (int32_t)lds_u32(idx_w + (4u * j + r4) * 4u);
+              cp_async16((dst_l + j * 512u) ^ ((j & 1u) << 6), x_lane + (size_t)(uint32_t)max(r, 0) * row_bytes,
+                         r >= 0 ? 16u : 0u);
+            }
+            cp_async_arrive_noinc_a(a_full_s);
+            __syncwarp();                            // every index has been consumed: now the slot may go
+            if (lane == 0) mbar_arrive_a(i_empty_k);
+            PROF_ADD(pg_iss, pg_t0);
+            PROF_INC(pg_n);
+          } else if ((mine >> k) & 1u) {
+            PROF_T0(pg_t0);
+            const uint32_t idx_k = idx_lane + ir.stage * (4u * kTileM * 4u) + team * (kTileM * 4u);
+            const int4 i0 = lds_v4(idx_k), i1 = lds_v4(idx_k + 16u);
+            const uint32_t sb = dst_lane + ar.stage * (4u * kTileBytes) + team * kTileBytes;
+            const int32_t ri[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              cp_async16(sb ^ (uint32_t)(i * 144), x_lane + (size_t)(uint32_t)max(ri[i], 0) * row_bytes,
+                         ri[i] >= 0 ? 16u : 0u);
+            cp_async_arrive_noinc_a(a_full_s);
+            __syncwarp();                            // the copies consumed the indices: now the slot may go
+            if (lane == 0) mbar_arrive_a(i_empty_k);
+            PROF_ADD(pg_iss, pg_t0);
+            PROF_INC(pg_n);
+          } else {
+            mbar_arrive_a(a_full_s);                 // nothing to gather: stand in for the cp.async arrivals
+            if (lane == 0) {
+              if (p.lean == 2) mbar_arrive_a(a_full_s);   // ... and for the warp's expect_tx arrival
+              mbar_arrive_a(i_empty_k);
+            }
+          }
+          ar.advance(S);
+          ir.advance(kIdxSlots);
+        }
+        ++it;
+        PROF_T0(pg_g0);
+      }
+    } else
     for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
       const int64_t tile0 = (int64_t)g * p.T;
       const uint32_t n_stages = fill_sched(sched, p, tile0, ntiles, lane) * nchunk;
-      if (!n_stages) continue;
+      PROF_ADD(pg_grp, pg_g0);
+      if (!n_stages) { PROF_T0(pg_g0); continue; }
       // offsets with work, as a bit mask in registers (sched[] itself is in shared memory)
       uint32_t any0, any1 = 0, any2 = 0, any3 = 0;
       any0 = __ballot_sync(0xffffffffu, lane < p.K && lds_u8(sched_s + (uint32_t)lane) != 0u);
@@ -486,6 +602,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
                 mbar_arrive_a(a_full_s);             // release: orders the ticket before the phase completes
               }
               if (!((bits >> t) & 1u)) {
+                PROF_T0(pg_t0);
                 mbar_arrive_a(a_full_s);             // nothing to gather: stand in for the cp.async arrivals
                 // The indices are not needed, but the team must still OBSERVE this phase of the
                 // slot's barrier: a parity wait is only sound for a waiter that has seen every
@@ -495,6 +612,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
                 // indices (seen as an illegal address with the T = 2 plan).
                 mbar_wait_warp_a(i_full_k, ir.phase);
                 if (lane == 0) mbar_arrive_a(i_empty_k);
+                PROF_ADD(pg_abs, pg_t0);
                 continue;
               }
               PROF_T0(pg_t0);
@@ -545,7 +663,9 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         }
       }
       ++it;
+      PROF_T0(pg_g0);
     }
+    if (lane == 0 && gw == 0) { PROF_PUT(28, PROF_NOW() - pg_start); PROF_PUT(29, pg_grp); PROF_PUT(30, pg_abs); }
     if (lane == 0 && q == 0) { PROF_PUT(8 + 4 * team, pg_we); PROF_PUT(9 + 4 * team, pg_wi); PROF_PUT(10 + 4 * team, pg_iss); PROF_PUT(11 + 4 * team, pg_n); }
     // the stage after the last one carries the END ticket
     for (uint32_t t = (team - nst * T) & 3u; t < T; t += 4) {
@@ -555,6 +675,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p) {
         mbar_arrive(&a_full[ar.stage]);
       }
       mbar_arrive(&a_full[ar.stage]);
+      if (p.lean == 2 && lane == 0) mbar_arrive(&a_full[ar.stage]);
     }
   } else if (warp >= kWarpMma0 && warp < kWarpMma0 + kMmaWarps) {
     // ===================== MMA issuers: driven by tickets =====================
@@ -824,6 +945,14 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
   p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots; p.b_merged = pl.b_merged; p.group_counter = group_counter;
   p.half_cols = pl.half_cols;
+  p.lean = (pl.T == 4 && pl.nchunk == 1 && pl.W == 1 && (c_in % 64) == 0 && !getenv("MK_TC_NOLEAN")) ? 1 : 0;
+  if (const char *e = getenv("MK_TC_LEAN")) p.lean = p.lean ? std::max(1, std::min(2, atoi(e))) : 0;   // development knob
+  CUtensorMap tmap_x;
+  memset(&tmap_x, 0, sizeof(tmap_x));
+  if (p.lean == 2) {      // the feature matrix as [n_in rows x 64 channels], one-row box: the tile::gather4 form
+    int rc = make_tmap_rows16(&tmap_x, std::is_same<T, __nv_bfloat16>::value ? MK_BF16 : MK_F16, x, n_in, c_in, 64, 1);
+    if (rc) return rc;
+  }
   const int64_t ntiles = (n_out + kTileM - 1) / kTileM;
   p.ngroups = (int)((ntiles + pl.T - 1) / pl.T);
   p.idesc = idesc_f16(fmt, kTileM, pl.NT, 0, 0);
@@ -837,9 +966,9 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   const int gx = (int)std::min<int64_t>((int64_t)p.ngroups, std::max(1, num_sms() / pl.nsplit));
   dim3 grid(gx, pl.nsplit);
   if (full)
-    k_conv_tc<T, true, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+    k_conv_tc<T, true, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p, tmap_x);
   else
-    k_conv_tc<T, false, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p);
+    k_conv_tc<T, false, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p, tmap_x);
   MK_LAUNCH_CHECK();
   return MK_OK;
 }

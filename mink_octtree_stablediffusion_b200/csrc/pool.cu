@@ -168,6 +168,7 @@ __global__ void k_global_bwd(int mode, const T *__restrict__ dy,
     const int64_t r = t / c;
     const int ch = (int)(t - r * c);
     const int32_t b = __ldg(batch_of_row + r);
+    if (b < 0) { dx[t] = from_acc<T, A>((A)0); continue; }   // row whose batch index has no origin row
     A v = to_acc<T>(dy[(size_t)b * c + ch]);
     if (mode == MK_POOL_AVG) v /= to_acc<T>(cnt[b]);
     if (mode == MK_POOL_MAX && argmax[(size_t)b * c + ch] != (int32_t)r) v = (A)0;
@@ -186,7 +187,9 @@ __global__ void k_broadcast_fwd(int mode, const T *__restrict__ x,
        t += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = t / c;
     const int ch = (int)(t - r * c);
-    const A gv = to_acc<T>(g[(size_t)__ldg(batch_of_row + r) * c + ch]);
+    const int32_t b = __ldg(batch_of_row + r);
+    // a row whose batch index has no origin row takes the operation's neutral element
+    const A gv = b >= 0 ? to_acc<T>(g[(size_t)b * c + ch]) : (mode == MK_BCAST_ADD ? (A)0 : (A)1);
     const A xv = to_acc<T>(x[t]);
     y[t] = from_acc<T, A>(mode == MK_BCAST_ADD ? xv + gv : xv * gv);
   }
@@ -204,8 +207,10 @@ __global__ void k_broadcast_bwd_dx(int mode, const T *__restrict__ g,
     const int64_t r = t / c;
     const int ch = (int)(t - r * c);
     A v = to_acc<T>(dy[t]);
-    if (mode == MK_BCAST_MUL)
-      v *= to_acc<T>(g[(size_t)__ldg(batch_of_row + r) * c + ch]);
+    if (mode == MK_BCAST_MUL) {
+      const int32_t b = __ldg(batch_of_row + r);
+      if (b >= 0) v *= to_acc<T>(g[(size_t)b * c + ch]);
+    }
     dx[t] = from_acc<T, A>(v);
   }
 }

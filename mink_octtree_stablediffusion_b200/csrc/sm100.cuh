@@ -166,6 +166,14 @@ __device__ __forceinline__ void sts_u32(uint32_t saddr, uint32_t v) {
 __device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_a(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void cp_async_arrive_noinc_a(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -229,6 +237,13 @@ __device__ __forceinline__ void tma_gather4(uint32_t dst_smem, const void *tmap,
       : "memory");
 }
 // plain 2-D tiled load: box at (col, row)
+__device__ __forceinline__ void tma_gather4_a(uint32_t dst_smem, const void *tmap, int32_t col, int4 r, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes.cta_group::1 "
+      "[%0], [%1, {%2, %3, %4, %5, %6}], [%7];" ::"r"(dst_smem),
+      "l"(tmap), "r"(col), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w), "r"(bar)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const void *tmap, int32_t col, int32_t row,
                                             uint64_t *bar) {
   asm volatile(

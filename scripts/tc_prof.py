@@ -28,7 +28,7 @@ perm, nbr_o = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])   # the product 
 mask_o = abi.tile_mask(nbr_o, n, ld, 27)
 names = {0: "epi wait t_full", 1: "epi work", 2: "idx wait i_empty", 3: "mma wait a_full", 4: "mma wait t_empty",
          5: "mma wait b_full", 6: "mma issue", 7: "mma stages", 24: "mma total", 25: "mma: proxy fence", 26: "mma: umma issue",
-         27: "mma: commits"}
+         27: "mma: commits", 28: "team0 total", 29: "team0 group fetch+sched", 30: "team0 absent tiles"}
 for t in range(4):
     names.update({8 + 4 * t: f"team{t} wait a_empty", 9 + 4 * t: f"team{t} wait i_full", 10 + 4 * t: f"team{t} issue",
                   11 + 4 * t: f"team{t} tiles"})

@@ -324,6 +324,39 @@ def test_tensor_core_plans_agree_under_load(monkeypatch):
             assert torch.equal(run(), ref), T
 
 
+def test_gather_loop_forms_agree(monkeypatch):
+    """The gather warps' three loop forms for Cin = 64, Cout <= 64, K <= 32 - the general loop
+    (MK_TC_NOLEAN), the lean loop (default) and the lean loop with TMA tile::gather4 for the fully
+    valid 4-row groups (MK_TC_LEAN=2) - move the same bytes: bit-identical outputs, forward (plain
+    and tile-ordered table) and data gradient (mirrored offsets), launch after launch."""
+    c = _northstar_cloud(120, "sorted")
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    perm, nbr_t = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])
+    mask = abi.tile_mask(nbr_t, n, ld, 27)
+    g = torch.Generator().manual_seed(29)
+    x = torch.randn(n, 64, generator=g).bfloat16().cuda()
+    runs = []
+    for cout in (64, 32):
+        w = (torch.randn(27, 64, cout, generator=g) / 40).bfloat16().cuda()
+        runs.append(lambda w=w: abi.conv_fwd_rows(x, w, nbr_t, ld, n, perm, mask=mask))
+        runs.append(lambda w=w: abi.conv_fwd(x, w, nbr, ld, n))
+    wt = (torch.randn(27, 64, 64, generator=g) / 40).bfloat16().cuda()
+    runs.append(lambda: abi.conv_fwd_rows(x, wt, nbr_t, ld, n, perm, transpose_w=1, kflip=1, mask=mask))
+    monkeypatch.delenv("MK_TC_LEAN", raising=False)
+    monkeypatch.setenv("MK_TC_NOLEAN", "1")
+    refs = [r() for r in runs]
+    assert abi.last_path() == 1
+    monkeypatch.delenv("MK_TC_NOLEAN")
+    for lean in ("1", "2"):
+        monkeypatch.setenv("MK_TC_LEAN", lean)
+        for _ in range(10):
+            for r, ref in zip(runs, refs):
+                assert torch.equal(r(), ref), lean
+
+
 @pytest.mark.parametrize("R,order,with_coords", [(60, "sorted", True), (60, "shuffled", True), (40, "sorted", False)])
 def test_tile_ordered_table(R, order, with_coords):
     """mk_kmap_tile_order: `order` is a permutation, the ordered table is the table with its
