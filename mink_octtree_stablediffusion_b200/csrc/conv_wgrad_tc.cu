@@ -82,6 +82,7 @@ struct Params {
   int a_stages, b_bufs;
   int ntiles, X;
   uint32_t idesc;
+  int shared_idx;         // pa even: the two panels of a pair are channel chunks of ONE offset and share an index slot
   int knock;   // development aid (MK_WG_KNOCK): 1 = no gather copies, 2 = no MMA
 };
 
@@ -176,7 +177,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], 256); mbar_init(&a_empty[s], kMmaWarps); }
     for (uint32_t s = 0; s < NBUF; ++s) mbar_init(&b_full[s], 1);
     for (uint32_t s = 0; s < NBUF * kMmaWarps; ++s) mbar_init(&b_empty[s], 1);
-    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], 4); }
+    for (int s = 0; s < kIdxSlots; ++s) { mbar_init(&i_full[s], 1); mbar_init(&i_empty[s], p.shared_idx ? 8 : 4); }
     for (int m = 0; m < kMmaWarps; ++m) mbar_init(&done[m], 2);
     *inited_slot = 0u;
     fence_barrier_init();
@@ -247,7 +248,9 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
         if (real) {
           // real panels before this one: both halves of the pairs below u, and the first half of u
           Ring is = ir;
-          is.skip((uint32_t)__popc(ts.p0 & below) + (uint32_t)__popc(ts.p1 & below) + (hf ? ((ts.p0 >> u) & 1u) : 0u),
+          is.skip(p.shared_idx ? (uint32_t)__popc(ts.pairs & below)
+                               : (uint32_t)__popc(ts.p0 & below) + (uint32_t)__popc(ts.p1 & below) +
+                                     (hf ? ((ts.p0 >> u) & 1u) : 0u),
                   kIdxSlots);
           WP_T0(g_t0);
           mbar_wait_warp_a(b_i_full + is.stage * 8u, is.phase);
@@ -280,7 +283,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
       const uint32_t n_st = (uint32_t)__popc(ts.pairs);
       nstage += n_st;
       ar.skip(n_st, S);
-      ir.skip((uint32_t)__popc(ts.p0) + (uint32_t)__popc(ts.p1), kIdxSlots);
+      ir.skip(p.shared_idx ? n_st : (uint32_t)__popc(ts.p0) + (uint32_t)__popc(ts.p1), kIdxSlots);
     }
     if (lane == 0 && (warp & 3) == 0) {
       WP_PUT(8 + 4 * team, g_wi); WP_PUT(9 + 4 * team, g_wa); WP_PUT(10 + 4 * team, g_is);
@@ -327,29 +330,47 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const UnitConst uc = unit_const(p, g, npair_cta, lane);
     uint32_t wn[4];
     load_mask(p, xs, wn);
+    WP_DECL(i_w = 0, i_t0 = 0, i_start = clock64(), i_n = 0, i_a = 0, i_b = 0, i_ta = 0, i_c = 0;)
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
+      WP_T0(i_ta);
       const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
       load_mask(p, tile + p.X, wn);
+      WP_DECL(i_tb = clock64();)
       const TileSched ts = tile_sched(p, w, uc);
-      // panel q = 2u + hf is real iff bit q of pm
-      uint32_t pm = 0;
-      for (int u = 0; u < npair_cta; ++u) pm |= (((ts.p0 >> u) & 1u) << (2 * u)) | (((ts.p1 >> u) & 1u) << (2 * u + 1));
+      WP_ADD(i_c, i_tb);
+      // Lane q owns panel q = 2u + hf (real iff bit q of pm) and the slot at its rank among the real
+      // panels.  (An earlier form gave lane i the i-th real panel through __fns and built pm in a loop
+      // over the units: ~3300 cycles per tile on this single warp, which a CTA of a wide layer - few
+      // units, so a tile every ~1500 cycles - could not hide: the gather teams waited for indices 41 %
+      // of the time at 256 -> 256.)
+      // With an even number of channel panels per offset (shared_idx) both panels of a pair read the
+      // same table row: one slot and one copy per PAIR, lane u = unit u with its own constants.
+      const uint32_t hf = p.shared_idx ? 0u : (uint32_t)lane & 1u;
+      const uint32_t pm = p.shared_idx
+                              ? ts.pairs
+                              : __ballot_sync(0xffffffffu, (((hf ? ts.p1 : ts.p0) >> (lane >> 1)) & 1u) != 0u);
       const uint32_t n = (uint32_t)__popc(pm);
-      const bool act = (uint32_t)lane < n;
-      const uint32_t q = act ? __fns(pm, 0, lane + 1) : 0u;
-      const int k0 = __shfl_sync(0xffffffffu, uc.k0, (int)(q >> 1)), k1 = __shfl_sync(0xffffffffu, uc.k1, (int)(q >> 1));
+      const bool act = (pm >> lane) & 1u;
+      const int src_lane = p.shared_idx ? lane : lane >> 1;
+      const int k0 = __shfl_sync(0xffffffffu, uc.k0, src_lane), k1 = __shfl_sync(0xffffffffu, uc.k1, src_lane);
+      WP_ADD(i_a, i_ta);
+      WP_T0(i_ta);
       if (act) {
-        const int k = (q & 1u) ? k1 : k0;
-        uint32_t slot = ir.stage + (uint32_t)lane, ph = ir.phase;
+        const int k = hf ? k1 : k0;
+        uint32_t slot = ir.stage + (uint32_t)__popc(pm & ((1u << lane) - 1u)), ph = ir.phase;
         if (slot >= (uint32_t)kIdxSlots) { slot -= kIdxSlots; ph ^= 1u; }
+        WP_T0(i_t0);
         mbar_wait(&i_empty[slot], ph ^ 1u);
+        WP_ADD(i_w, i_t0);
         const int32_t *src = p.nbr + (int64_t)k * p.ld + (int64_t)tile * kTileM;
         mbar_arrive_expect_tx(&i_full[slot], kTileM * 4);
         bulk_g2s(i_base + slot * (kTileM * 4), src, kTileM * 4, &i_full[slot]);
       }
       __syncwarp();
+      WP_ADD(i_b, i_ta);
       ir.skip(n, kIdxSlots);
     }
+    if (lane == 0) { WP_PUT(25, i_w); WP_ELAPSED(i_start); WP_PUT(26, i_start); WP_PUT(27, i_a); WP_PUT(28, i_b); WP_PUT(29, i_c); }
   } else if (warp >= kWarpMma && warp < kWarpMma + kMmaWarps) {
     // ===================== MMA issuers =====================
     // The serial cost of a stage on the issuing warp (barrier wait, proxy fence,
@@ -440,12 +461,16 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     const UnitConst uc = unit_const(p, g, npair_cta, lane);
     uint32_t wn[4];
     load_mask(p, xs, wn);
+    WP_DECL(d_we = 0, d_ld = 0, d_t0 = 0, d_start = clock64(), d_n = 0;)
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
       const uint32_t w[4] = {wn[0], wn[1], wn[2], wn[3]};
       load_mask(p, tile + p.X, wn);
       const TileSched ts = tile_sched(p, w, uc);
       if (!ts.pairs) continue;
+      WP_T0(d_t0);
       for (int m = 0; m < kMmaWarps; ++m) mbar_wait_warp(&b_empty[br.stage * kMmaWarps + m], br.phase ^ 1u);
+      WP_ADD(d_we, d_t0);
+      WP_T0(d_t0);
       if (p.dy_rows) {
         // rows through the permutation: lane l brings rows 4l..4l+3 of the tile with one
         // tile::gather4 per 64-channel panel (same swizzled image as the tiled load);
@@ -473,8 +498,10 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
                       tile * kTileM, &b_full[br.stage]);
       }
       __syncwarp();
+      WP_ADD(d_ld, d_t0);
       br.advance(NBUF);
     }
+    if (lane == 0) { WP_PUT(6, d_we); WP_PUT(7, d_ld); WP_ELAPSED(d_start); WP_PUT(24, d_start); }
   }
 
 done_role:
@@ -518,6 +545,26 @@ k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t n, T *__restric
   dw[i + 3] = from_acc<T, float>(acc.w);
 }
 
+// out[i, :] = dy[rows[i], :] (16-bit rows of `row_bytes`, a multiple of 16), 16 bytes per thread.
+// For wide outputs the weight-gradient kernel reads dy tiles with one tiled TMA load per panel from
+// this copy instead of 32 tile::gather4 per panel through the permutation: a CTA of a wide layer needs
+// a new dy tile every ~1300 cycles (few units per CTA, so few stages per tile), and the single loader
+// warp's gather4 stream took ~4500 (measured: 63 % of the MMA warps' time waiting for the dy tile at
+// 256 -> 256; 4.68 -> 3.2 ms + 0.2 ms for this pass).
+__global__ void __launch_bounds__(256)
+k_gather_rows16(const uint8_t *__restrict__ dy, const int32_t *__restrict__ rows, int64_t n, int row_bytes,
+                uint8_t *__restrict__ out) {
+  const int per_row = row_bytes >> 4;
+  const int64_t total = n * per_row;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = t / per_row;
+    const int c = (int)(t - r * per_row);
+    const int64_t src = (int64_t)__ldg(rows + r);
+    reinterpret_cast<uint4 *>(out + r * row_bytes)[c] =
+        __ldg(reinterpret_cast<const uint4 *>(dy + src * row_bytes) + c);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
@@ -537,8 +584,14 @@ static int arm_hang_report() {
 namespace {
 struct WPlan {
   int pa, npairs, nsplit, NB, nbpad, pb, U, G, ppg, a_stages, b_bufs, ntiles, X, W;
-  size_t smem, partial_bytes, mask_bytes;
+  size_t smem, partial_bytes, mask_bytes, dyg_bytes;
 };
+
+// dy through a tile order: pre-gathered copy (wide outputs) or tile::gather4 inside the kernel (narrow)
+inline bool pregather_dy(int c_out) {
+  if (const char *e = getenv("MK_WG_PREGATHER")) return atoi(e) != 0;   // development knob
+  return c_out >= 128;
+}
 
 inline size_t align256w(size_t b) { return (b + 255) & ~(size_t)255; }
 
@@ -582,6 +635,7 @@ bool make_wplan(int dtype, int64_t n_out, int K, int c_in, int c_out, WPlan &pl)
   pl.smem = fixed + pl.b_bufs * b_tile + (size_t)pl.a_stages * kStageBytes;
   pl.partial_bytes = align256w((size_t)pl.X * K * c_in * c_out * 4);
   pl.mask_bytes = align256w((size_t)pl.ntiles * pl.W * 4);
+  pl.dyg_bytes = pregather_dy(c_out) ? align256w((size_t)n_out * c_out * 2) : 0;
   return true;
 }
 }  // namespace
@@ -603,7 +657,7 @@ int64_t conv_wgrad_tc_rows_per_cta(int64_t n_out, int K, int c_in, int c_out) {
 int64_t conv_wgrad_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
   WPlan pl;
   if (!make_wplan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return 0;
-  return (int64_t)(pl.partial_bytes + pl.mask_bytes + 256);
+  return (int64_t)(pl.partial_bytes + pl.mask_bytes + pl.dyg_bytes + 256);
 }
 
 int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_rows, const int32_t *nbr,
@@ -623,6 +677,15 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_ro
     if (rc) return rc;
     tile_mask = mask;
   }
+  if (dy_rows && pl.dyg_bytes) {
+    uint8_t *dyg = ws + pl.partial_bytes + pl.mask_bytes;
+    const int64_t total = n_out * (int64_t)(c_out * 2 / 16);
+    const unsigned blocks = (unsigned)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 16);
+    k_gather_rows16<<<blocks, 256, 0, st>>>((const uint8_t *)dy, dy_rows, n_out, c_out * 2, dyg);
+    MK_LAUNCH_CHECK();
+    dy = dyg;
+    dy_rows = nullptr;
+  }
   CUtensorMap tmap_dy, tmap_dy_row;
   {
     int rc = make_tmap_rows16(&tmap_dy, dtype, dy, n_out, c_out, 64, kTileM);
@@ -639,6 +702,7 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_ro
   p.a_stages = pl.a_stages; p.b_bufs = pl.b_bufs;
   p.ntiles = pl.ntiles; p.X = pl.X;
   p.idesc = idesc_f16(dtype == MK_BF16 ? 1 : 0, kTileM, pl.NB, 1, 1);
+  p.shared_idx = (pl.pa % 2 == 0 && !getenv("MK_WG_NOSHARE")) ? 1 : 0;
   p.knock = getenv("MK_WG_KNOCK") ? atoi(getenv("MK_WG_KNOCK")) : 0;
   { int rc = arm_hang_report(); if (rc) return rc; }
   MK_CUDA(cudaFuncSetAttribute(k_conv_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));

@@ -22,11 +22,13 @@ c = sphere(271)
 n = len(c)
 tin = abi.insert(c)
 nbr, ld, counts = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offsets3())
-x = torch.randn(n, 64).bfloat16().cuda()
-dy = torch.randn(n, 64).bfloat16().cuda()
+CIN = int(os.environ.get("WG_CIN", "64"))
+COUT = int(os.environ.get("WG_COUT", "64"))
+x = torch.randn(n, CIN).bfloat16().cuda()
+dy = torch.randn(n, COUT).bfloat16().cuda()
 perm, nbr_o = abi.tile_order(nbr, n, ld, 27, tin["coords_dev"])   # the product layout
 mask_o = abi.tile_mask(nbr_o, n, ld, 27)
-names = {0: "mma wait b_full", 1: "mma wait a_full", 2: "mma issue", 3: "mma loop total", 4: "team0 in-panel block", 5: "team0 tile sched"}
+names = {0: "mma wait b_full", 1: "mma wait a_full", 2: "mma issue", 3: "mma loop total", 4: "team0 in-panel block", 5: "team0 tile sched", 6: "dy loader wait b_empty", 7: "dy loader index + issue", 24: "dy loader total", 25: "idx lane0 wait i_empty", 26: "idx total", 27: "idx: mask + schedule", 28: "idx: waits + copies (all lanes)", 29: "idx: tile_sched only"}
 for t in range(4):
     names.update({8 + 4 * t: f"team{t} wait i_full", 9 + 4 * t: f"team{t} wait a_empty", 10 + 4 * t: f"team{t} issue",
                   11 + 4 * t: f"team{t} loop total"})
@@ -47,6 +49,8 @@ for kn in sys.argv[1:] or ["0"]:
         v = buf[:, k]
         print(f"  {names[k]:22s} {v.mean() / 1e3:10.1f}  (min {v.min() / 1e3:.1f} max {v.max() / 1e3:.1f})")
     # loop total per pair group (blockIdx.y = the two halves of buf) and its spread over the tile splits
+    if (CIN, COUT) != (64, 64):
+        continue
     tot = buf[:, 3].reshape(2, -1) / 1e3
     for y in range(2):
         print(f"  pair group {y}: mma loop total mean {tot[y].mean():.1f} min {tot[y].min():.1f} max {tot[y].max():.1f}; "
