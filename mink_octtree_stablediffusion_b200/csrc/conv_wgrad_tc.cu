@@ -131,7 +131,7 @@ struct TileSched { uint32_t pairs, p0, p1; };
 
 __device__ __forceinline__ void load_mask(const Params &p, int tile, uint32_t (&w)[4]) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) w[i] = (i < p.W && tile < p.ntiles) ? __ldg(p.mask + (int64_t)tile * p.W + i) : 0u;
+  for (int i = 0; i < 4; ++i) w[i] = (i < p.W && (unsigned)tile < (unsigned)p.ntiles) ? __ldg(p.mask + (int64_t)tile * p.W + i) : 0u;
 }
 
 __device__ __forceinline__ TileSched tile_sched(const Params &p, const uint32_t (&w)[4], const UnitConst &c) {
@@ -602,7 +602,11 @@ bool make_wplan(int dtype, int64_t n_out, int K, int c_in, int c_out, WPlan &pl)
   if (n_out > (int64_t)kTileM * 0x7fffff00) return false;
   pl.pa = (c_in + 63) / 64;
   pl.npairs = (K * pl.pa + 1) / 2;
-  int nb_max = 128;   // 128-column accumulators: dy tile of 32 KB, four A stages in flight (256: 64 KB tile, two stages; 512 -> 512 wgrad 325 -> 508 TFLOP/s)
+  // 128-column accumulators: dy tile of 32 KB, four A stages in flight.  From 512 output channels on, 256
+  // columns (64 KB dy tile, two A stages): every gathered panel is then used for twice the columns
+  // (512 -> 512 on a dense 48^3 cube 817 -> 1015 TFLOP/s, on the sphere surface 400 -> 415; at 256 -> 256
+  // the sphere loses 5 %).
+  int nb_max = c_out >= 512 ? 256 : 128;
   if (const char *e = getenv("MK_WG_NB")) nb_max = std::max(16, std::min(256, atoi(e)));   // development knob
   int nsplit = (c_out + nb_max - 1) / nb_max;
   while (c_out % (16 * nsplit)) ++nsplit;
