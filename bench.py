@@ -561,11 +561,11 @@ def run_engine(args):
             "roofline": {"bound": "tensor", "kernel": "conv forward (%s)" % ("tcgen05" if conv_path else "simt"),
                          "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
                          # dram__bytes_read+write of one k_conv_tc launch at R=271 on the tile-ordered table,
-                         # ncu --set full (profiles/r1f_ncu_full_conv_final.csv); algorithmic bytes
-                         # are x + y + neighbour table + output-row permutation
-                         "traffic": 306.0e6 if (conv_path and R == R_FULL) else None,
-                         "traffic_source": "ncu --set full capture profiles/r1f_ncu_full_conv_final.csv (2^7 blocks), "
-                                           "not measured in this run",
+                         # ncu --set full (profiles/r2b_ncu_full_conv64.csv: 204.9 MB read + 95.9 MB written);
+                         # algorithmic bytes are x + y + neighbour table + output-row permutation
+                         "traffic": 300.8e6 if (conv_path and R == R_FULL) else None,
+                         "traffic_source": "ncu --set full capture profiles/r2b_ncu_full_conv64.csv (same kernel, "
+                                           "same cloud), not measured in this run",
                          "alg_bytes_per_launch": int(n * (C_IN + C_OUT) * 2 + 4 * KS ** 3 * n + 4 * n),
                          "peak_source": pk["source"] + " (burst bf16 matmul)",
                          "useful_flops_per_launch": flops_pass},
