@@ -179,7 +179,7 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": info["cores"], "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------
@@ -598,7 +598,7 @@ def run_engine(args):
             line["cfg1"] = cfg1
         if vae is not None:
             line["vae"] = vae
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -726,6 +726,20 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
             **out}
 
 
+_JSON_FD = None
+
+
+def emit(line) -> None:
+    """Write the result line to the real stdout (see main)."""
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -745,6 +759,12 @@ def main():
     ap.add_argument("--vae-dtypes", default="bf16,fp32_tc,fp32")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    # stdout carries exactly ONE line, the JSON: everything libraries print on the way (NCCL's version
+    # banner goes to stdout) is sent to stderr by pointing fd 1 at fd 2 until the line is written
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
