@@ -104,6 +104,19 @@ def _fused_instance_norm(x: SparseTensor, coef_fn, params):
     return segment_norm(F_, seg, nb, counts.to(_acc(F_)), coef_fn, params, shift=shift)
 
 
+def _fused_group_norm(x: SparseTensor, weight, bias, eps, gs: int, gw: int):
+    """Instance / group norm with its coefficient algebra in one launch each way (csrc/norm.cu
+    `mk_gn_coef_fwd/bwd`): statistics over a batch item's rows and `gs` adjacent channels, affine
+    parameters shared by `gw` adjacent channels."""
+    from mink_octtree_stablediffusion_b200.backend_norm import group_instance_norm
+    seg, nb, counts, first = _segments(x)
+    F_ = x.F
+    acc = _acc(F_)
+    shift = F_.detach()[first].to(acc).contiguous()
+    return group_instance_norm(F_, seg, nb, counts if counts.dtype == acc else counts.to(acc), shift, weight, bias,
+                               eps, gs, gw)
+
+
 def _fold_group(stat, group):
     if group == 1:
         return stat
@@ -232,7 +245,7 @@ class MinkowskiInstanceNorm(MinkowskiModuleBase):
     def forward(self, input: SparseTensor):
         assert isinstance(input, SparseTensor)
         if input.F.is_cuda:
-            return _like(input, _fused_instance_norm(input, _stable_coef(self.eps, lambda s: s), (self.weight, self.bias)))
+            return _like(input, _fused_group_norm(input, self.weight, self.bias, self.eps, 1, 1))
         y = _instance_standardise(input, self.eps)
         return _like(input, y * self.weight + self.bias)
 
@@ -276,12 +289,7 @@ class MinkowskiStableInstanceNorm(MinkowskiModuleBase):
 
     def forward(self, x):
         if x.F.is_cuda:
-            g = self.group
-
-            def coef(mean, var, weight, bias):
-                return _stable_coef(self.eps, self._fold)(mean, var, torch.repeat_interleave(weight, g, dim=-1),
-                                                           torch.repeat_interleave(bias, g, dim=-1))
-            return _like(x, _fused_instance_norm(x, coef, (self.weight, self.bias)))
+            return _like(x, _fused_group_norm(x, self.weight, self.bias, self.eps, self.group, self.group))
         y = _instance_standardise(x, self.eps, self._fold)
         scale = torch.repeat_interleave(self.weight, self.group, dim=-1)
         shift = torch.repeat_interleave(self.bias, self.group, dim=-1)
@@ -315,7 +323,7 @@ class MinkowskiStableGroupNorm(MinkowskiModuleBase):
     def forward(self, x):
         fold = lambda s: s.mean(dim=1, keepdim=True).repeat(1, self.num_features)  # noqa: E731
         if x.F.is_cuda:
-            return _like(x, _fused_instance_norm(x, _stable_coef(self.eps, fold), (self.weight, self.bias)))
+            return _like(x, _fused_group_norm(x, self.weight, self.bias, self.eps, self.num_features, 1))
         y = _instance_standardise(x, self.eps, fold)
         return _like(x, y * self.weight + self.bias)
 

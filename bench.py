@@ -538,6 +538,16 @@ def run_engine(args):
             if world > 1:
                 raise
 
+    # ---- the other example networks (BASELINE configs[2] and [3]), single GPU only ---------------
+    nets = None
+    if world == 1 and not args.no_extra and not args.no_nets:
+        gc.collect()
+        torch.cuda.empty_cache()
+        try:
+            nets = run_nets_leg(args, dev, lib)
+        except Exception as e:
+            nets = {"error": f"{type(e).__name__}: {e}"}
+
     # ---- reduce over ranks -----------------------------------------------------
     t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms, ms_h2d], dtype=torch.float64, device=dev)
     if world > 1:
@@ -598,6 +608,8 @@ def run_engine(args):
             line["cfg1"] = cfg1
         if vae is not None:
             line["vae"] = vae
+        if nets is not None:
+            line["nets"] = nets
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -726,6 +738,76 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
             **out}
 
 
+def run_nets_leg(args, dev, lib):
+    """Forward + backward of the reference's unchanged MinkUNet34C (examples/minkunet.py:193; BASELINE
+    configs[2]: 1 M-voxel scene, bf16) and diffusion UNet (examples/diffusion.py:89; configs[3]: stride-8
+    latents of 256^3 G3 octrees, unet_channel (4, 320, 640, 960), bf16) on the engine: ms per step with
+    the coordinate maps rebuilt every step (a new SparseTensor per step, as a training loop does)."""
+    import torch
+    import MinkowskiEngine as ME
+    from harness import workloads as W
+    from oracle import oracle as O
+
+    def timed(step, warm=3, it=5):
+        for _ in range(warm):
+            step()
+        torch.cuda.synchronize()
+        l0 = int(lib.mk_launch_count())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(it):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / it, float(loss), (int(lib.mk_launch_count()) - l0) // it
+
+    out = {}
+    torch.manual_seed(0)
+    mu = W.load_minkunet()
+    net = mu.MinkUNet34C(3, 20, D=3).to(dev).to(torch.bfloat16)
+    c = torch.from_numpy(O.sphere_surface(R_FULL, 0, 0)).to(dev)
+    f = torch.rand(len(c), 3, device=dev).to(torch.bfloat16)
+    labels = torch.randint(0, 20, (len(c),), device=dev)
+    crit = torch.nn.CrossEntropyLoss()
+
+    def step_mu():
+        net.zero_grad(set_to_none=True)
+        y = net(ME.SparseTensor(f, c))
+        loss = crit(y.F.float(), labels)
+        loss.backward()
+        return loss
+
+    ms, loss, nl = timed(step_mu)
+    out["minkunet34c"] = {"workload": "examples/minkunet.py MinkUNet34C(3, 20) fwd+bwd, bf16, sphere surface R=271",
+                          "voxels": int(len(c)), "ms_per_step": ms, "voxels_per_s": len(c) / (ms * 1e-3),
+                          "loss": loss, "engine_launches_per_step": nl}
+    del net, c, f, labels
+    torch.cuda.empty_cache()
+
+    cfg = W.diffusion_config(resolution=256, batch_size=4)
+    d = W.load_unet(cfg)
+    torch.manual_seed(0)
+    unet = d.UNet(cfg.unet_channel, cfg).to(dev).to(torch.bfloat16)
+    lat = torch.from_numpy(O.stride_coords(W.batched(W.g3_batch(256, 4)), [8, 8, 8])).to(dev)
+    xf = torch.randn(len(lat), 4, device=dev).to(torch.bfloat16)
+    noise = torch.randn(len(lat), 4, device=dev).to(torch.bfloat16)
+    tt = torch.randint(0, 1000, (4,), device=dev)
+
+    def step_un():
+        unet.zero_grad(set_to_none=True)
+        y = unet(ME.SparseTensor(xf, lat, tensor_stride=8), tt)
+        loss = torch.nn.functional.mse_loss(y.F.float(), noise.float())
+        loss.backward()
+        return loss
+
+    ms, loss, nl = timed(step_un)
+    out["diffusion_unet"] = {"workload": "examples/diffusion.py UNet((4, 320, 640, 960)) fwd+bwd (one DDPM training "
+                                         "step's network pass), bf16, stride-8 latents of 4 G3 octrees @ 256^3",
+                             "latent_voxels": int(len(lat)), "ms_per_step": ms, "steps_per_s": 1e3 / ms,
+                             "loss": loss, "engine_launches_per_step": nl}
+    return out
+
+
 _JSON_FD = None
 
 
@@ -750,6 +832,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vae", action="store_true", help="skip the VAE steps/s leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the wide-layer rooflines and the cfg1 leg")
+    ap.add_argument("--no-nets", action="store_true", help="skip the MinkUNet34C / diffusion UNet leg")
     ap.add_argument("--no-bind", action="store_true", help="do not bind the ranks to their GPUs' host cores")
     ap.add_argument("--no-vae-profile", action="store_true")
     ap.add_argument("--vae-steps", type=int, default=10)

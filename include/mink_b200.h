@@ -379,6 +379,20 @@ int mk_bn_coef_bwd(int acc_f64, const void *sums, const void *mean, const void *
                    double count_host, const void *weight, int c, void *coef_a, void *coef_b, void *coef_c,
                    void *dweight, void *dbias, void *stream);
 
+/* Instance / group norm coefficients in one launch each way (MinkowskiInstanceNorm,
+ * MinkowskiStableInstanceNorm, MinkowskiStableGroupNorm: MinkowskiNormalization.py:198-478).  Per
+ * batch item the statistics are taken over the item's rows and `gs` adjacent channels; weight / bias
+ * [c / gw] are shared by `gw` adjacent channels.  Arrays are of the accumulator type; sums [n_seg, 2, c],
+ * shift / coefficients / mean [n_seg, c], mu / inv [n_seg, c / gs], counts [n_seg].
+ *   fwd: sums = mk_seg_sums(x, x, shift, shift, seg)  -> y = coef_a[seg] x + coef_c[seg]
+ *   bwd: sums = mk_seg_sums(dy, x, NULL, mean, seg)   -> dx = coef_a dy + coef_b x + coef_c, dweight, dbias */
+int mk_gn_coef_fwd(int acc_f64, const void *sums, const void *shift, const void *counts, const void *weight,
+                   const void *bias, double eps, int c, int gs, int gw, int64_t n_seg, void *coef_a, void *coef_c,
+                   void *mean_out, void *mu_out, void *inv_out, void *stream);
+int mk_gn_coef_bwd(int acc_f64, const void *sums, const void *mean, const void *mu, const void *inv,
+                   const void *counts, const void *weight, int c, int gs, int gw, int64_t n_seg, void *coef_a,
+                   void *coef_b, void *coef_c, void *dweight, void *dbias, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,6 +76,8 @@ PROTOTYPES = {
     "mk_bn_coef_fwd": (_i, [_i, _p, _p, _p, C.c_double, _p, _p, C.c_double, _i, _p, _p, _p, _p, _p, _p, C.c_double, _p]),
     "mk_bn_coef_bwd": (_i, [_i, _p, _p, _p, _p, C.c_double, _p, _i, _p, _p, _p, _p, _p, _p]),
     "mk_seg_affine": (_i, [_i, _p, _p, _p, _i64, _i, _p, _p, _p, _p, _p]),
+    "mk_gn_coef_fwd": (_i, [_i, _p, _p, _p, _p, _p, C.c_double, _i, _i, _i, _i64, _p, _p, _p, _p, _p, _p]),
+    "mk_gn_coef_bwd": (_i, [_i, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _p, _p, _p, _p, _p, _p]),
 }
 
 _lib = None

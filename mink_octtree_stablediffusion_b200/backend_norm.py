@@ -201,3 +201,64 @@ def batch_norm_train(x, weight, bias, running_mean, running_var, momentum, eps, 
     """weight / bias / running statistics must be of the accumulator dtype (float32, or float64 for
     float64 features); reduce_fn(flat_tensor) all-reduces in place."""
     return _BatchNormTrain.apply(x, weight, bias, running_mean, running_var, momentum, eps, reduce_fn)
+
+
+# ---------------------------------------------------------------------------
+# instance / group norm: the two passes with the [n_seg, C] algebra in one launch each way
+# ---------------------------------------------------------------------------
+class _GroupInstanceNorm(torch.autograd.Function):
+    """Per batch item, statistics over the item's rows and `gs` adjacent channels; weight / bias
+    shared by `gw` adjacent channels (MinkowskiInstanceNorm gs = gw = 1, MinkowskiStableInstanceNorm
+    gs = gw = group, MinkowskiStableGroupNorm gs = C, gw = 1; reference MinkowskiNormalization.py:198-478).
+    The same result as `segment_norm` with the layers' coefficient functions (tested against it), with
+    six launches per norm and pass instead of ~100."""
+
+    @staticmethod
+    def forward(ctx, x, seg, n_seg, counts, shift, weight, bias, eps, gs, gw):
+        lib = _lib.load()
+        x = x.contiguous()
+        n, c = x.shape
+        acc = _acc_dtype(x)
+        f64 = int(acc == torch.float64)
+        S = seg_sums(x, x, shift, shift, seg, n_seg)
+        w = weight.detach().reshape(-1).to(acc).contiguous() if weight is not None else None
+        b = bias.detach().reshape(-1).to(acc).contiguous() if bias is not None else None
+        buf = torch.empty((3, n_seg, c), dtype=acc, device=x.device)          # A, C, mean
+        stat = torch.empty((2, n_seg, c // gs), dtype=acc, device=x.device)   # mu, inv
+        _lib.check(lib.mk_gn_coef_fwd(f64, _ptr(S), _ptr(shift), _ptr(counts), _ptr(w), _ptr(b), float(eps), c, gs, gw,
+                                      n_seg, _ptr(buf[0]), _ptr(buf[1]), _ptr(buf[2]), _ptr(stat[0]), _ptr(stat[1]),
+                                      _stream()))
+        y = seg_affine(x, None, seg, buf[0], None, buf[1])
+        ctx.save_for_backward(x, seg, buf, stat, counts, w if w is not None else torch.empty(0))
+        ctx.meta = (n_seg, gs, gw, weight.shape if weight is not None else None, weight.dtype if weight is not None else None,
+                    bias.shape if bias is not None else None, bias.dtype if bias is not None else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x, seg, buf, stat, counts, w = ctx.saved_tensors
+        n_seg, gs, gw, w_shape, w_dtype, b_shape, b_dtype = ctx.meta
+        dy = dy.contiguous()
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        n, c = x.shape
+        acc = buf.dtype
+        mean = buf[2]
+        S = seg_sums(dy, x, None, mean, seg, n_seg)
+        co = torch.empty((3, n_seg, c), dtype=acc, device=x.device)
+        need_w, need_b = w_shape is not None and ctx.needs_input_grad[5], b_shape is not None and ctx.needs_input_grad[6]
+        dwb = torch.empty((2, c // gw), dtype=acc, device=x.device) if (need_w or need_b) else None
+        _lib.check(lib.mk_gn_coef_bwd(int(acc == torch.float64), _ptr(S), _ptr(mean), _ptr(stat[0]), _ptr(stat[1]),
+                                      _ptr(counts), _ptr(w) if w.numel() else None, c, gs, gw, n_seg, _ptr(co[0]),
+                                      _ptr(co[1]), _ptr(co[2]), _ptr(dwb[0]) if need_w else None,
+                                      _ptr(dwb[1]) if need_b else None, _stream()))
+        dx = seg_affine(dy, x, seg, co[0], co[1], co[2]) if ctx.needs_input_grad[0] else None
+        dw = dwb[0].to(w_dtype).view(w_shape) if need_w else None
+        db = dwb[1].to(b_dtype).view(b_shape) if need_b else None
+        return (dx, None, None, None, None, dw, db, None, None, None)
+
+
+def group_instance_norm(x, seg, n_seg, counts, shift, weight, bias, eps, gs, gw):
+    """counts / shift: accumulator dtype (float32, or float64 for float64 features)."""
+    return _GroupInstanceNorm.apply(x, seg, n_seg, counts, shift, weight, bias, eps, gs, gw)

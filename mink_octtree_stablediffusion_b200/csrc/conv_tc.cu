@@ -91,6 +91,7 @@ struct ConvTCParams {
   int b_merged;           // weight ring = A ring (same depth): image s travels with stage s on the stage's barriers
   int c_in, c_out, nchunk, NT, T;
   int a_stages, b_stages, i_slots;
+  int ksplit, kper;       // offsets split over blockIdx.z (small maps): CTA z serves schedule positions [z kper, (z+1) kper)
   int lean;               // gather warps: the lean loop (T == 4, one channel chunk, one mask word per tile)
   int half_cols;          // TMEM columns between the two accumulator halves: 256, or 0 = one accumulator set only
                           // (wide outputs: twice the tiles per group, i.e. per weight image, instead of an
@@ -140,6 +141,41 @@ __global__ void k_pack_b(const T *__restrict__ w, int transpose, int K, int c_re
   }
 }
 
+// The same image for transpose == 0 through a shared-memory tile: W[k][c][n] is contiguous along n, the
+// image along c, so the element-wise kernel above reads 2 bytes per 32-byte sector (64 us for the 50 MB of
+// a 27 x 960 x 960 kernel, 13 % of the kernel time of a diffusion-UNet step).  One block = 64 channels x
+// 64 output columns of one offset: coalesced reads along n, 16-byte writes along c.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_pack_b_tiled(const T *__restrict__ w, int K, int c_red, int c_n, int nchunk, int NT, int nsplit,
+               T *__restrict__ out, int *__restrict__ group_counter) {
+  __shared__ T tile[64][66];
+  if (group_counter && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (int)threadIdx.x < nsplit)
+    group_counter[threadIdx.x] = 0;
+  const int ng0 = blockIdx.x * 64, ch = blockIdx.y, k = blockIdx.z;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+#pragma unroll
+  for (int r = 0; r < 16; ++r) {
+    const int cl = r * 4 + ty;
+    const int c = ch * 64 + cl, ng = ng0 + tx;
+    tile[cl][tx] = (c < c_red && ng < c_n) ? w[((size_t)k * c_red + c) * c_n + ng] : T(0.f);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int idx = (int)threadIdx.x + j * 256;
+    const int nl = idx >> 3, chunk = idx & 7;
+    const int ng = ng0 + nl;
+    if (ng >= nsplit * NT) continue;
+    const int sp = ng / NT, n = ng - sp * NT;
+    alignas(16) T v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = tile[chunk * 8 + i][nl];
+    const size_t base = ((((size_t)sp * K + k) * nchunk + ch) * NT + n) * 64;
+    *reinterpret_cast<uint4 *>(out + base + ((chunk ^ (n & 7)) << 3)) = *reinterpret_cast<const uint4 *>(v);
+  }
+}
+
 // mask[tile*W + k/32] bit k%32 = any(nbr[k, 128*tile .. 128*tile+127] >= 0)
 __global__ void k_tile_mask(const int32_t *__restrict__ nbr, int64_t n_rows, int64_t ld, int K, int W,
                             uint32_t *__restrict__ mask) {
@@ -179,18 +215,28 @@ __device__ __forceinline__ uint32_t fill_sched(uint8_t *sched, const ConvTCParam
                                                int64_t ntiles, int lane) {
   __syncwarp();
   uint32_t cnt = 0;
+  const int kz0 = (int)blockIdx.z * p.kper, kz1 = min(p.K, kz0 + p.kper);
   for (int k = lane; k < p.K; k += 32) {
     const int kk = p.kflip ? p.K - 1 - k : k;
     uint32_t bits = 0;
     for (int t = 0; t < p.T; ++t) {
       const int64_t tile = tile0 + t;
-      if (tile < ntiles) bits |= ((__ldg(p.mask + tile * p.W + (kk >> 5)) >> (kk & 31)) & 1u) << t;
+      if (tile < ntiles && k >= kz0 && k < kz1) bits |= ((__ldg(p.mask + tile * p.W + (kk >> 5)) >> (kk & 31)) & 1u) << t;
     }
     sched[k] = (uint8_t)bits;
     cnt += bits ? 1u : 0u;
   }
   __syncwarp();
   return __reduce_add_sync(0xffffffffu, cnt);   // number of offsets with any neighbour in the group
+}
+
+// Bits of mask word `wi` (table offsets 32 wi .. 32 wi + 31) that this CTA's share of the offsets covers
+__device__ __forceinline__ uint32_t subset_word(const ConvTCParams &p, int wi) {
+  const int kz0 = (int)blockIdx.z * p.kper, kz1 = min(p.K, kz0 + p.kper);
+  const int lo = (p.kflip ? p.K - kz1 : kz0) - 32 * wi, hi = (p.kflip ? p.K - kz0 : kz1) - 32 * wi;
+  const int a = max(lo, 0), b = min(hi, 32);
+  if (b <= a) return 0u;
+  return (b == 32 ? 0xffffffffu : (1u << b) - 1u) & ~((1u << a) - 1u);
 }
 
 // Queue through which the index warp tells the other roles which group comes next (dynamic
@@ -309,7 +355,8 @@ k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtens
   // out in table order, so concurrently processed groups stay neighbours in L2, but a CTA
   // that drew cheap groups simply takes more of them (static: the slowest CTA of the
   // north-star layer carried 9 % more stages than the mean).
-  GroupQueue gq_ctl{gq, gq_full, gq_empty, p.group_counter ? p.group_counter + blockIdx.y : nullptr, p.ngroups};
+  GroupQueue gq_ctl{gq, gq_full, gq_empty,
+                    p.group_counter ? p.group_counter + blockIdx.z * gridDim.y + blockIdx.y : nullptr, p.ngroups};
 
   if (threadIdx.x == 0) {
     for (uint32_t s = 0; s < S; ++s) { mbar_init(&a_full[s], (uint32_t)p.T * (p.lean == 2 ? 132u : 128u) + 1u + (p.b_merged ? 1u : 0u)); mbar_init(&a_empty[s], kMmaWarps); }
@@ -336,7 +383,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtens
       uint32_t any = 0;
       for (int t = 0; t < p.T; ++t)
         if (tile0 + t < ntiles)
-          for (int wi = 0; wi < p.W; ++wi) any |= __ldg(p.mask + (tile0 + t) * p.W + wi);
+          for (int wi = 0; wi < p.W; ++wi) any |= __ldg(p.mask + (tile0 + t) * p.W + wi) & subset_word(p, wi);
       if (any) {
         PROF_T0(pe_t0);
         mbar_wait_warp(&t_full[h], (it >> 1) & 1u, 3, 400);   // outermost wait: report inner stalls first
@@ -348,10 +395,10 @@ k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtens
         const int64_t tile = tile0 + t;
         if (tile >= ntiles) break;
         uint32_t touched = 0;
-        for (int wi = 0; wi < p.W; ++wi) touched |= __ldg(p.mask + tile * p.W + wi);
+        for (int wi = 0; wi < p.W; ++wi) touched |= __ldg(p.mask + tile * p.W + wi) & subset_word(p, wi);
         const int64_t row = tile * kTileM + warp * 32 + lane;   // table column
         const int64_t orow = (p.out_rows && row < p.n_out) ? (int64_t)__ldg(p.out_rows + row) : row;
-        TOut *yrow = (TOut *)p.y + (size_t)orow * p.c_out + (size_t)sp * p.NT;
+        TOut *yrow = (TOut *)p.y + ((size_t)blockIdx.z * p.n_out + (size_t)orow) * p.c_out + (size_t)sp * p.NT;
         const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * p.half_cols + t * acc_stride);
         for (int c0 = 0; c0 < p.NT; c0 += 16) {
           uint32_t v[16];
@@ -454,6 +501,8 @@ k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtens
       // registers: no schedule copy in shared memory, no ballots, no nested loops.  (The general loop
       // spends ~350 instructions per warp and stage at one instruction per ~6 cycles, of which 8 are
       // copies: the gather warps' own chain, not the copy rate, set the stage period - DESIGN 4.9.)
+      const int kz0 = (int)blockIdx.z * p.kper, kz1 = min(p.K, kz0 + p.kper);
+      const uint32_t kz_mask = (kz1 >= 32 ? 0xffffffffu : (1u << kz1) - 1u) & ~((1u << kz0) - 1u);
       for (int g = gq_ctl.first(role_is_idx, lane); g >= 0; g = gq_ctl.next(role_is_idx, lane, g)) {
         const int64_t tile0 = (int64_t)g * 4;
         uint32_t mm[4];
@@ -461,7 +510,7 @@ k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtens
         for (int j = 0; j < 4; ++j) {
           uint32_t v = tile0 + j < ntiles ? __ldg(p.mask + tile0 + j) : 0u;
           if (p.kflip) v = __brev(v) >> (32 - p.K);     // schedule position k <-> table offset K-1-k
-          mm[j] = v;
+          mm[j] = v & kz_mask;
         }
         const uint32_t all = mm[0] | mm[1] | mm[2] | mm[3];
         PROF_ADD(pg_grp, pg_g0);
@@ -802,6 +851,27 @@ k_conv_tc(const __grid_constant__ ConvTCParams p, const __grid_constant__ CUtens
   }
 }
 
+// y[i] = sum_z part[z][i] in the fixed order z = 0, 1, ... (n is a multiple of 16: c_out is)
+template <typename TOut>
+__global__ void __launch_bounds__(256)
+k_ksplit_reduce(const float *__restrict__ part, int ks, int64_t n, TOut *__restrict__ y) {
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += (int64_t)gridDim.x * blockDim.x * 4) {
+    float4 a = __ldg(reinterpret_cast<const float4 *>(part + i));
+    for (int z = 1; z < ks; ++z) {
+      const float4 v = __ldg(reinterpret_cast<const float4 *>(part + (size_t)z * n + i));
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    if constexpr (sizeof(TOut) == 4) {
+      *reinterpret_cast<float4 *>(y + i) = a;
+    } else {
+      uint2 o;
+      o.x = pack2<TOut>(a.x, a.y);
+      o.y = pack2<TOut>(a.z, a.w);
+      *reinterpret_cast<uint2 *>(y + i) = o;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
@@ -821,13 +891,14 @@ static int arm_hang_report() {
 
 struct TCPlan {
   int nsplit, NT, nchunk, T, W, a_stages, b_stages, i_slots, b_merged, half_cols;
-  size_t smem, bpack_bytes, mask_bytes, range_bytes;
+  int ksplit, kper;       // offsets split over grid.z with fp32 partial outputs (small maps), else 1 / K
+  size_t smem, bpack_bytes, mask_bytes, range_bytes, part_bytes;
 };
 
 static inline size_t align256s(size_t b) { return (b + 255) & ~(size_t)255; }
 
 // One candidate: T tiles per group on accumulator halves `half_cols` apart (0 = a single set).
-static bool plan_with(int64_t n_out, int K, int c_in, int c_out, int T, int half_cols, TCPlan &pl) {
+static bool plan_with(int dtype, int64_t n_out, int K, int c_in, int c_out, int T, int half_cols, TCPlan &pl) {
   int nsplit = (c_out + 255) / 256;
   while (c_out % (16 * nsplit)) ++nsplit;
   pl.nsplit = nsplit;
@@ -868,7 +939,25 @@ static bool plan_with(int64_t n_out, int K, int c_in, int c_out, int T, int half
   pl.smem = fixed + (size_t)S * stage_bytes;
   pl.bpack_bytes = align256s((size_t)nsplit * K * pl.nchunk * b_bytes);
   pl.mask_bytes = align256s((size_t)((n_out + kTileM - 1) / kTileM) * pl.W * 4);
-  pl.range_bytes = 256;   // group counters, one int per output split
+  pl.range_bytes = 256;   // group counters, one int per output split (and offset split)
+  // Small maps: a layer with fewer groups than SMs leaves most of the GPU idle while a handful of CTAs
+  // stream ALL K weight images (27 x 960 x 960 on a 206-row latent map: 8 CTAs, 335 us).  The offsets
+  // are then split over grid.z; every CTA writes an fp32 partial output and a second kernel adds them in
+  // a fixed order.  Partials are bounded by the SM count: <= 148 x T x 128 rows x NT columns x 4 B.
+  pl.ksplit = 1;
+  pl.kper = K;
+  pl.part_bytes = 0;
+  const int64_t ngroups = ((n_out + kTileM - 1) / kTileM + pl.T - 1) / pl.T;
+  const int64_t ctas = ngroups * pl.nsplit;
+  if (dtype == MK_BF16 && K >= 2 && ctas * 2 <= num_sms() && !getenv("MK_TC_NOKSPLIT")) {
+    int ks = (int)std::min<int64_t>(K, num_sms() / ctas);
+    ks = std::min(ks, 64 / pl.nsplit);
+    if (ks >= 2) {
+      pl.kper = (K + ks - 1) / ks;
+      pl.ksplit = (K + pl.kper - 1) / pl.kper;
+      pl.part_bytes = align256s((size_t)pl.ksplit * n_out * c_out * 4);
+    }
+  }
   return true;
 }
 
@@ -892,8 +981,8 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   // four tiles do not fit the ring, and three on one set measured slower than two on each of two sets).
   if (!getenv("MK_TC_TWO_SETS"))
     for (int t = t_one; t >= 2 * t_two; --t)
-      if (plan_with(n_out, K, c_in, c_out, t, 0, pl)) return true;
-  return plan_with(n_out, K, c_in, c_out, t_two, 256, pl);
+      if (plan_with(dtype, n_out, K, c_in, c_out, t, 0, pl)) return true;
+  return plan_with(dtype, n_out, K, c_in, c_out, t_two, 256, pl);
 }
 
 bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) {
@@ -904,7 +993,7 @@ bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out) 
 int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out) {
   TCPlan pl;
   if (!make_plan(MK_BF16, std::max<int64_t>(n_out, 1), K, c_in, c_out, pl)) return 0;
-  return (int64_t)(pl.bpack_bytes + pl.mask_bytes + pl.range_bytes + 256);
+  return (int64_t)(pl.bpack_bytes + pl.mask_bytes + pl.range_bytes + pl.part_bytes + 256);
 }
 
 int tile_mask_launch(const int32_t *nbr, int64_t n_rows, int64_t ld, int K, uint32_t *mask, cudaStream_t st) {
@@ -928,9 +1017,15 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   int *group_counter = getenv("MK_TC_STATIC") ? nullptr : (int *)(ws + pl.bpack_bytes + pl.mask_bytes);
   {
     const int64_t total = (int64_t)pl.nsplit * K * pl.nchunk * pl.NT * 64;
-    const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 8);
-    k_pack_b<T><<<blocks, 256, 0, st>>>((const T *)w, transpose_w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit,
-                                        bpack, group_counter);
+    if (!transpose_w && !getenv("MK_TC_PACK_FLAT")) {
+      dim3 pg((unsigned)ceil_div(pl.nsplit * pl.NT, 64), (unsigned)pl.nchunk, (unsigned)K);
+      k_pack_b_tiled<T><<<pg, 256, 0, st>>>((const T *)w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit, bpack,
+                                            group_counter);
+    } else {
+      const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 8);
+      k_pack_b<T><<<blocks, 256, 0, st>>>((const T *)w, transpose_w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit,
+                                          bpack, group_counter);
+    }
     MK_LAUNCH_CHECK();
   }
   if (tile_mask == nullptr) {
@@ -945,6 +1040,10 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
   p.c_in = c_in; p.c_out = c_out; p.nchunk = pl.nchunk; p.NT = pl.NT; p.T = pl.T;
   p.a_stages = pl.a_stages; p.b_stages = pl.b_stages; p.i_slots = pl.i_slots; p.b_merged = pl.b_merged; p.group_counter = group_counter;
   p.half_cols = pl.half_cols;
+  p.ksplit = pl.ksplit;
+  p.kper = pl.kper;
+  if (pl.ksplit > 1 && group_counter)   // one counter per (offset split, output split); k_pack_b zeroed the first nsplit
+    MK_CUDA(cudaMemsetAsync(group_counter, 0, sizeof(int) * pl.nsplit * pl.ksplit, st));
   p.lean = (pl.T == 4 && pl.nchunk == 1 && pl.W == 1 && (c_in % 64) == 0 && !getenv("MK_TC_NOLEAN")) ? 1 : 0;
   if (const char *e = getenv("MK_TC_LEAN")) p.lean = p.lean ? std::max(1, std::min(2, atoi(e))) : 0;   // development knob
   CUtensorMap tmap_x;
@@ -963,8 +1062,8 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
     MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, true, TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   else
     MK_CUDA(cudaFuncSetAttribute(k_conv_tc<T, false, TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  const int gx = (int)std::min<int64_t>((int64_t)p.ngroups, std::max(1, num_sms() / pl.nsplit));
-  dim3 grid(gx, pl.nsplit);
+  const int gx = (int)std::min<int64_t>((int64_t)p.ngroups, std::max(1, num_sms() / (pl.nsplit * pl.ksplit)));
+  dim3 grid(gx, pl.nsplit, pl.ksplit);
   if (full)
     k_conv_tc<T, true, TOut><<<grid, kNumThreadsTC, pl.smem, st>>>(p, tmap_x);
   else
@@ -980,6 +1079,20 @@ int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kf
   if (!make_plan(dtype, n_out, K, c_in, c_out, pl)) {
     set_error("conv_fwd_tc: shape not eligible");
     return MK_EUNSUPPORTED;
+  }
+  if (dtype == MK_BF16 && pl.ksplit > 1) {
+    float *part = (float *)((uint8_t *)workspace + pl.bpack_bytes + pl.mask_bytes + pl.range_bytes);
+    int rc = conv_fwd_tc_typed<__nv_bfloat16, float>(pl, 1, x, w, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in,
+                                                     K, c_in, c_out, part, out_rows, workspace, st);
+    if (rc) return rc;
+    const int64_t n_el = n_out * (int64_t)c_out;
+    const unsigned blocks = (unsigned)std::min<int64_t>(ceil_div(n_el / 4, 256), (int64_t)num_sms() * 16);
+    if (out_f32)
+      k_ksplit_reduce<float><<<blocks, 256, 0, st>>>(part, pl.ksplit, n_el, (float *)y);
+    else
+      k_ksplit_reduce<__nv_bfloat16><<<blocks, 256, 0, st>>>(part, pl.ksplit, n_el, (__nv_bfloat16 *)y);
+    MK_LAUNCH_CHECK();
+    return MK_OK;
   }
   if (dtype == MK_BF16) {
     if (out_f32)

@@ -347,6 +347,112 @@ int seg_affine_t(const void *a, const void *b, const int32_t *seg, int64_t n, in
 
 using namespace mk;
 
+// ---------------------------------------------------------------------------
+// Instance / group norm coefficients (MinkowskiInstanceNorm, MinkowskiStableInstanceNorm,
+// MinkowskiStableGroupNorm: MinkowskiNormalization.py:198-478 of the reference).  Per batch item s
+// the statistics are taken over the item's rows and the `gs` adjacent channels of a statistics
+// group G; the affine parameters are shared by `gw` adjacent channels (weight / bias [C / gw]).
+//   forward:  per channel mean_c, var_c from S = sums of (x - K), (x - K)^2;
+//             mu_G = avg_c mean_c,  v_G = avg_c (var_c + (mean_c - mu_G)^2),  inv = rsqrt(v_G + eps)
+//             y = A x + C,  A = inv w,  C = b - mu_G A
+//   backward: S = sums of dy, dy (x - mean_c);  P0 = sum_c w S0_c,
+//             P1 = sum_c w inv (S1_c + (mean_c - mu_G) S0_c),  M = m gs
+//             dx = A dy + cB x + cC,  cB = -inv^2 P1 / M,  cC = -inv P0 / M - cB mu_G
+//             dweight_j = sum_s sum_{c in j} inv (S1_c + (mean_c - mu) S0_c),  dbias_j = sum_s sum_{c in j} S0_c
+// One thread per (batch item, statistics group); these are [n_seg, C]-sized problems - the point is
+// ONE launch instead of the ~40 tiny torch kernels of the same algebra (a diffusion-UNet step holds
+// 102 such norms and was bound by their launches).
+template <typename A>
+__global__ void k_gn_coef_fwd(const A *__restrict__ S, const A *__restrict__ shift, const A *__restrict__ counts,
+                              const A *__restrict__ weight, const A *__restrict__ bias, double eps, int c, int gs,
+                              int gw, int n_seg, A *__restrict__ coef_a, A *__restrict__ coef_c,
+                              A *__restrict__ mean_out, A *__restrict__ mu_out, A *__restrict__ inv_out) {
+  const int ng = c / gs;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_seg * ng) return;
+  const int s = t / ng, g = t - s * ng;
+  const A m = max(counts[s], (A)1);
+  const A *s0 = S + (size_t)s * 2 * c, *s1 = s0 + c;
+  A mu = 0;
+  for (int i = 0; i < gs; ++i) {
+    const int ch = g * gs + i;
+    const A mean = (shift ? shift[(size_t)s * c + ch] : (A)0) + s0[ch] / m;
+    mean_out[(size_t)s * c + ch] = mean;
+    mu += mean;
+  }
+  mu /= (A)gs;
+  A v = 0;
+  for (int i = 0; i < gs; ++i) {
+    const int ch = g * gs + i;
+    const A d = s0[ch] / m;
+    A var = s1[ch] / m - d * d;
+    var = var > (A)0 ? var : (A)0;
+    const A dm = (shift ? shift[(size_t)s * c + ch] : (A)0) + d - mu;
+    v += var + dm * dm;
+  }
+  v /= (A)gs;
+  const A inv = (A)1 / sqrt(v + (A)eps);
+  mu_out[t] = mu;
+  inv_out[t] = inv;
+  for (int i = 0; i < gs; ++i) {
+    const int ch = g * gs + i;
+    const A a = inv * (weight ? weight[ch / gw] : (A)1);
+    coef_a[(size_t)s * c + ch] = a;
+    coef_c[(size_t)s * c + ch] = (bias ? bias[ch / gw] : (A)0) - mu * a;
+  }
+}
+
+template <typename A>
+__global__ void k_gn_coef_bwd(const A *__restrict__ S, const A *__restrict__ mean, const A *__restrict__ mu_in,
+                              const A *__restrict__ inv_in, const A *__restrict__ counts, const A *__restrict__ weight,
+                              int c, int gs, int gw, int n_seg, A *__restrict__ coef_a, A *__restrict__ coef_b,
+                              A *__restrict__ coef_c) {
+  const int ng = c / gs;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_seg * ng) return;
+  const int s = t / ng, g = t - s * ng;
+  const A M = max(counts[s], (A)1) * (A)gs;
+  const A mu = mu_in[t], inv = inv_in[t];
+  const A *s0 = S + (size_t)s * 2 * c, *s1 = s0 + c;
+  A p0 = 0, p1 = 0;
+  for (int i = 0; i < gs; ++i) {
+    const int ch = g * gs + i;
+    const A w = weight ? weight[ch / gw] : (A)1;
+    p0 += w * s0[ch];
+    p1 += w * inv * (s1[ch] + (mean[(size_t)s * c + ch] - mu) * s0[ch]);
+  }
+  const A cb = -inv * inv * p1 / M;
+  const A cc = -inv * p0 / M - cb * mu;
+  for (int i = 0; i < gs; ++i) {
+    const int ch = g * gs + i;
+    coef_a[(size_t)s * c + ch] = inv * (weight ? weight[ch / gw] : (A)1);
+    coef_b[(size_t)s * c + ch] = cb;
+    coef_c[(size_t)s * c + ch] = cc;
+  }
+}
+
+// parameter gradients: one thread per weight index j (the channels [j gw, (j+1) gw) of every batch item)
+template <typename A>
+__global__ void k_gn_param_grads(const A *__restrict__ S, const A *__restrict__ mean, const A *__restrict__ mu_in,
+                                 const A *__restrict__ inv_in, int c, int gs, int gw, int n_seg,
+                                 A *__restrict__ dweight, A *__restrict__ dbias) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= c / gw) return;
+  const int ng = c / gs;
+  A dw = 0, db = 0;
+  for (int s = 0; s < n_seg; ++s) {
+    const A *s0 = S + (size_t)s * 2 * c, *s1 = s0 + c;
+    for (int i = 0; i < gw; ++i) {
+      const int ch = j * gw + i;
+      const int t = s * ng + ch / gs;
+      dw += inv_in[t] * (s1[ch] + (mean[(size_t)s * c + ch] - mu_in[t]) * s0[ch]);
+      db += s0[ch];
+    }
+  }
+  if (dweight) dweight[j] = dw;
+  if (dbias) dbias[j] = db;
+}
+
 extern "C" {
 
 int mk_seg_sums(int dtype, const void *a, const void *b, const void *shift_a, const void *shift_b,
@@ -402,6 +508,61 @@ int mk_bn_coef_bwd(int acc_f64, const void *sums, const void *mean, const void *
     k_bn_coef_bwd<float><<<grid, 128, 0, (cudaStream_t)stream>>>(
         (const float *)sums, (const float *)mean, (const float *)invstd, (const float *)count_dev, count_host,
         (const float *)weight, c, (float *)coef_a, (float *)coef_b, (float *)coef_c, (float *)dweight, (float *)dbias);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+int mk_gn_coef_fwd(int acc_f64, const void *sums, const void *shift, const void *counts, const void *weight,
+                   const void *bias, double eps, int c, int gs, int gw, int64_t n_seg, void *coef_a, void *coef_c,
+                   void *mean_out, void *mu_out, void *inv_out, void *stream) {
+  MK_CHECK_ARG(c >= 1 && gs >= 1 && gw >= 1 && c % gs == 0 && c % gw == 0 && n_seg >= 0, "bad channel grouping");
+  MK_CHECK_ARG(n_seg <= (1 << 20), "too many segments");
+  if (n_seg == 0) return MK_OK;
+  MK_CHECK_ARG(sums && counts && coef_a && coef_c && mean_out && mu_out && inv_out, "null pointer");
+  const unsigned grid = (unsigned)ceil_div((int64_t)n_seg * (c / gs), 128);
+  if (acc_f64)
+    k_gn_coef_fwd<double><<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const double *)sums, (const double *)shift, (const double *)counts, (const double *)weight,
+        (const double *)bias, eps, c, gs, gw, (int)n_seg, (double *)coef_a, (double *)coef_c, (double *)mean_out,
+        (double *)mu_out, (double *)inv_out);
+  else
+    k_gn_coef_fwd<float><<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const float *)sums, (const float *)shift, (const float *)counts, (const float *)weight, (const float *)bias,
+        eps, c, gs, gw, (int)n_seg, (float *)coef_a, (float *)coef_c, (float *)mean_out, (float *)mu_out,
+        (float *)inv_out);
+  MK_LAUNCH_CHECK();
+  return MK_OK;
+}
+
+int mk_gn_coef_bwd(int acc_f64, const void *sums, const void *mean, const void *mu, const void *inv,
+                   const void *counts, const void *weight, int c, int gs, int gw, int64_t n_seg, void *coef_a,
+                   void *coef_b, void *coef_c, void *dweight, void *dbias, void *stream) {
+  MK_CHECK_ARG(c >= 1 && gs >= 1 && gw >= 1 && c % gs == 0 && c % gw == 0 && n_seg >= 0, "bad channel grouping");
+  MK_CHECK_ARG(n_seg <= (1 << 20), "too many segments");
+  MK_CHECK_ARG(sums && mean && mu && inv && counts && coef_a && coef_b && coef_c, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)std::max<int64_t>(1, ceil_div((int64_t)n_seg * (c / gs), 128));
+  const unsigned gridp = (unsigned)ceil_div(c / gw, 128);
+  if (acc_f64) {
+    if (n_seg)
+      k_gn_coef_bwd<double><<<grid, 128, 0, st>>>((const double *)sums, (const double *)mean, (const double *)mu,
+                                                  (const double *)inv, (const double *)counts, (const double *)weight,
+                                                  c, gs, gw, (int)n_seg, (double *)coef_a, (double *)coef_b,
+                                                  (double *)coef_c);
+    if (dweight || dbias)
+      k_gn_param_grads<double><<<gridp, 128, 0, st>>>((const double *)sums, (const double *)mean, (const double *)mu,
+                                                      (const double *)inv, c, gs, gw, (int)n_seg, (double *)dweight,
+                                                      (double *)dbias);
+  } else {
+    if (n_seg)
+      k_gn_coef_bwd<float><<<grid, 128, 0, st>>>((const float *)sums, (const float *)mean, (const float *)mu,
+                                                 (const float *)inv, (const float *)counts, (const float *)weight, c,
+                                                 gs, gw, (int)n_seg, (float *)coef_a, (float *)coef_b, (float *)coef_c);
+    if (dweight || dbias)
+      k_gn_param_grads<float><<<gridp, 128, 0, st>>>((const float *)sums, (const float *)mean, (const float *)mu,
+                                                     (const float *)inv, c, gs, gw, (int)n_seg, (float *)dweight,
+                                                     (float *)dbias);
+  }
   MK_LAUNCH_CHECK();
   return MK_OK;
 }

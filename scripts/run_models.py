@@ -148,6 +148,19 @@ def run_unet(a):
 
     print("[unet] loss", float(step()), flush=True)
     print("[unet] step times (s):", [round(t, 4) for t in timed(step, a.steps)])
+    if a.profile:
+        profile(step, "unet")
+    if a.cprofile:
+        import cProfile
+        import pstats
+        pr = cProfile.Profile()
+        pr.enable()
+        step()
+        torch.cuda.synchronize()
+        pr.disable()
+        st = pstats.Stats(pr)
+        st.sort_stats("cumulative").print_stats(70)
+        st.sort_stats("tottime").print_stats(40)
 
 
 if __name__ == "__main__":
