@@ -49,14 +49,14 @@ def _fused_batch_norm(bn: torch.nn.modules.batchnorm._BatchNorm, x: torch.Tensor
     """Training-mode batch norm of the feature matrix (statistics over all rows; for
     SyncBatchNorm over the rows of all ranks), running statistics updated like torch's
     (`momentum`, unbiased running variance).  Returns None when the case is not served
-    (eval mode, no rows, parameters not of the accumulator dtype) and the caller uses torch's own."""
+    (eval mode, no rows, parameters on another device) and the caller uses torch's own."""
     from mink_octtree_stablediffusion_b200.backend_norm import batch_norm_train
     use_batch_stats = bn.training or not bn.track_running_stats or bn.running_mean is None
     if not use_batch_stats or x.shape[0] == 0 or not x.is_floating_point():
         return None
     acc = _acc(x)
     tensors = [t for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var) if t is not None]
-    if any(t.dtype != acc or t.device != x.device for t in tensors):
+    if any(not t.is_floating_point() or t.device != x.device for t in tensors):
         return None
     reduce_fn = None
     if sync_group is not False:

@@ -145,6 +145,15 @@ class _BatchNormTrain(torch.autograd.Function):
         dev = x.device
         buf = torch.empty((7, c), dtype=acc, device=dev)      # sums[2], A, C, mean, invstd, shift
         sums, coef_a, coef_c, mean, invstd, shift = buf[0:2], buf[2], buf[3], buf[4], buf[5], buf[6]
+        # parameters / running statistics of a 16-bit module (net.to(bfloat16)): the algebra runs on
+        # accumulator-dtype copies, the running statistics are written back in their own dtype
+        w_in, rm_in, rv_in = weight, running_mean, running_var
+        if weight is not None and weight.dtype != acc:
+            weight = weight.detach().to(acc)
+        if bias is not None and bias.dtype != acc:
+            bias = bias.detach().to(acc)
+        if running_mean is not None and running_mean.dtype != acc:
+            running_mean, running_var = running_mean.to(acc), running_var.to(acc)
         count_dev = None
         if reduce_fn is None:
             shift.copy_(x[0])                                 # any value near the mean centres the one-pass sums
@@ -163,10 +172,14 @@ class _BatchNormTrain(torch.autograd.Function):
                                       float(eps), c, _ptr(coef_a), _ptr(coef_c), _ptr(mean), _ptr(invstd),
                                       _ptr(running_mean) if upd else None, _ptr(running_var) if upd else None,
                                       float(momentum or 0.0), _stream()))
+        if upd and rm_in is not running_mean:
+            rm_in.copy_(running_mean)
+            rv_in.copy_(running_var)
         y = seg_affine(x, None, None, coef_a, None, coef_c)
         ctx.save_for_backward(x, weight, mean, invstd, count_dev if count_dev is not None else torch.empty(0))
         ctx.reduce_fn, ctx.n = reduce_fn, n
         ctx.has_bias = bias is not None
+        ctx.param_dtype = w_in.dtype if w_in is not None else (bias.dtype if bias is not None else acc)
         return y
 
     @staticmethod
@@ -194,11 +207,13 @@ class _BatchNormTrain(torch.autograd.Function):
             import torch.distributed as dist
             w = dist.get_world_size()
             dw, db = dw / w, db / w
+        if ctx.param_dtype != acc:
+            dw, db = dw.to(ctx.param_dtype), db.to(ctx.param_dtype)
         return (dx, dw if weight is not None else None, db if ctx.has_bias else None, None, None, None, None, None)
 
 
 def batch_norm_train(x, weight, bias, running_mean, running_var, momentum, eps, reduce_fn=None):
-    """weight / bias / running statistics must be of the accumulator dtype (float32, or float64 for
+    """weight / bias / running statistics: any floating dtype (the algebra runs in float32, or float64 for
     float64 features); reduce_fn(flat_tensor) all-reduces in place."""
     return _BatchNormTrain.apply(x, weight, bias, running_mean, running_var, momentum, eps, reduce_fn)
 

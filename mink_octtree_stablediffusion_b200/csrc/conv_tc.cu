@@ -141,6 +141,31 @@ __global__ void k_pack_b(const T *__restrict__ w, int transpose, int K, int c_re
   }
 }
 
+// transpose == 1 (data gradient: B(n, c) = W[k][n0 + n][c], contiguous along c like the image): one thread
+// per 16-byte chunk, 32-bit index arithmetic (the element-wise kernel spends ~100 instructions of 64-bit
+// division per 2-byte element: 64 us for a 27 x 960 x 960 kernel).
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_pack_b_rows(const T *__restrict__ w, int K, int c_red, int c_n, int nchunk, int NT, int nsplit, T *__restrict__ out,
+              int *__restrict__ group_counter) {
+  if (group_counter && blockIdx.x == 0 && (int)threadIdx.x < nsplit) group_counter[threadIdx.x] = 0;
+  const uint32_t total = (uint32_t)nsplit * K * nchunk * NT * 8u;
+  for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const uint32_t chunk = e & 7u;
+    uint32_t r = e >> 3;
+    const uint32_t n = r % (uint32_t)NT; r /= (uint32_t)NT;
+    const uint32_t ch = r % (uint32_t)nchunk; r /= (uint32_t)nchunk;
+    const uint32_t k = r % (uint32_t)K;
+    const uint32_t sp = r / (uint32_t)K;
+    const uint32_t c0 = ch * 64u + chunk * 8u, ng = sp * (uint32_t)NT + n;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (c0 < (uint32_t)c_red && ng < (uint32_t)c_n)   // c_red is a multiple of 16: a chunk is whole or absent
+      v = __ldg(reinterpret_cast<const uint4 *>(w + ((size_t)k * c_n + ng) * c_red + c0));
+    const size_t base = ((((size_t)sp * K + k) * nchunk + ch) * NT + n) * 64;
+    *reinterpret_cast<uint4 *>(out + base + ((chunk ^ (n & 7u)) << 3)) = v;
+  }
+}
+
 // The same image for transpose == 0 through a shared-memory tile: W[k][c][n] is contiguous along n, the
 // image along c, so the element-wise kernel above reads 2 bytes per 32-byte sector (64 us for the 50 MB of
 // a 27 x 960 x 960 kernel, 13 % of the kernel time of a diffusion-UNet step).  One block = 64 channels x
@@ -1021,6 +1046,11 @@ static int conv_fwd_tc_typed(const TCPlan &pl, int fmt, const void *x, const voi
       dim3 pg((unsigned)ceil_div(pl.nsplit * pl.NT, 64), (unsigned)pl.nchunk, (unsigned)K);
       k_pack_b_tiled<T><<<pg, 256, 0, st>>>((const T *)w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit, bpack,
                                             group_counter);
+    } else if (transpose_w && (c_in % 8) == 0 && ((uintptr_t)w & 15) == 0 && total / 8 < (1ll << 31) &&
+               !getenv("MK_TC_PACK_FLAT")) {
+      const int blocks = (int)std::min<int64_t>(ceil_div(total / 8, 256), (int64_t)num_sms() * 8);
+      k_pack_b_rows<T><<<blocks, 256, 0, st>>>((const T *)w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit, bpack,
+                                               group_counter);
     } else {
       const int blocks = (int)std::min<int64_t>(ceil_div(total, 256), (int64_t)num_sms() * 8);
       k_pack_b<T><<<blocks, 256, 0, st>>>((const T *)w, transpose_w, K, c_in, c_out, pl.nchunk, pl.NT, pl.nsplit,

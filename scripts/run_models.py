@@ -119,6 +119,8 @@ def run_minkunet(a):
 
     print("[minkunet] loss", float(step()), flush=True)
     print("[minkunet] step times (s):", [round(t, 4) for t in timed(step, a.steps)])
+    if a.profile:
+        profile(step, "minkunet")
 
 
 def run_unet(a):

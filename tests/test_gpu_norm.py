@@ -96,6 +96,44 @@ def test_batch_norm_matches_torch(dtype, c):
     assert rel(bn(ME.SparseTensor(xin.detach(), coords)).F, ref(xr.detach())) <= TOL[dtype] * 3
 
 
+def test_batch_norm_of_a_16_bit_module():
+    """net.to(torch.bfloat16) (how scripts/run_models.py and the MinkUNet bench leg run): parameters and
+    running statistics are bf16 too; the fused passes must serve them (fp32 algebra, statistics written
+    back in bf16) and agree with an fp64 BatchNorm1d on the same rounded values."""
+    import MinkowskiEngine as ME
+    from mink_octtree_stablediffusion_b200 import backend_norm
+    coords = torch.from_numpy(O.sphere_surface(14, 0, 0)).cuda()
+    n, c = len(coords), 64
+    torch.manual_seed(5)
+    bn = ME.MinkowskiBatchNorm(c)
+    with torch.no_grad():
+        bn.bn.weight.uniform_(0.5, 1.5)
+        bn.bn.bias.uniform_(-1, 1)
+    bn = bn.to(torch.bfloat16).cuda()
+    ref = torch.nn.BatchNorm1d(c).double()
+    ref.load_state_dict({k: v.double().cpu() if v.is_floating_point() else v.cpu() for k, v in bn.bn.state_dict().items()})
+    x = (torch.randn(n, c) * 2 + 3).bfloat16().cuda().requires_grad_(True)
+    xr = x.detach().double().cpu().requires_grad_(True)
+    dy = torch.randn(n, c).bfloat16()
+    calls = []
+    orig = backend_norm.batch_norm_train
+    backend_norm.batch_norm_train = lambda *a, **k: (calls.append(1), orig(*a, **k))[1]
+    try:
+        out = bn(ME.SparseTensor(x, coords))
+    finally:
+        backend_norm.batch_norm_train = orig
+    assert calls, "the fused path must serve 16-bit parameters"
+    yr = ref(xr)
+    assert out.F.dtype == torch.bfloat16 and rel(out.F, yr) <= 1e-2
+    out.F.backward(dy.cuda())
+    yr.backward(dy.double())
+    assert rel(x.grad, xr.grad) <= 2e-2
+    assert bn.bn.weight.grad.dtype == torch.bfloat16 and rel(bn.bn.weight.grad, ref.weight.grad) <= 1e-2
+    assert rel(bn.bn.bias.grad, ref.bias.grad) <= 1e-2
+    assert bn.bn.running_mean.dtype == torch.bfloat16 and rel(bn.bn.running_mean, ref.running_mean) <= 1e-2
+    assert rel(bn.bn.running_var, ref.running_var) <= 1e-2
+
+
 def _norm_case(make, with_emb=False, c=32):
     """module on the GPU (fused passes) vs the same module on CPU tensors over the oracle backend (composed)."""
     import MinkowskiEngine as ME
