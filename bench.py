@@ -525,6 +525,16 @@ def run_engine(args):
                 "cpu_ref_fwd_bwd_ms": float(np.median(tc_)) * 1e3, "cpu_ref_voxels_per_s": len(c1) / float(np.median(tc_)),
                 "cpu_cores": CR.num_threads(), "conv_path": "tcgen05 (bf16 x3 split)" if lib.mk_conv_last_path() else "simt"}
 
+    # ---- the other example networks (BASELINE configs[2] and [3]), single GPU only ---------------
+    nets = None
+    if world == 1 and not args.no_extra and not args.no_nets:
+        gc.collect()
+        torch.cuda.empty_cache()
+        try:
+            nets = run_nets_leg(args, dev, lib)
+        except Exception as e:
+            nets = {"error": f"{type(e).__name__}: {e}"}
+
     # ---- VAE leg (the other half of BASELINE.json's metric) ---------------------
     vae = None
     if not args.no_vae:
@@ -537,16 +547,6 @@ def run_engine(args):
             vae = {"error": f"{type(e).__name__}: {e}"}
             if world > 1:
                 raise
-
-    # ---- the other example networks (BASELINE configs[2] and [3]), single GPU only ---------------
-    nets = None
-    if world == 1 and not args.no_extra and not args.no_nets:
-        gc.collect()
-        torch.cuda.empty_cache()
-        try:
-            nets = run_nets_leg(args, dev, lib)
-        except Exception as e:
-            nets = {"error": f"{type(e).__name__}: {e}"}
 
     # ---- reduce over ranks -----------------------------------------------------
     t = torch.tensor([ms_total, ms_e2e, fwd_ms, bwd_ms, ms_h2d], dtype=torch.float64, device=dev)
