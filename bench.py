@@ -732,7 +732,7 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
                         f"vae_channel (32,128,512,512,4)", "voxels_per_gpu": n_vox, "scaling": "weak",
             "h2d_bytes_per_step": int(coords_h.numel() * 4), "steps": steps, "warmup": warmup,
             "host": "gc.freeze() after warm-up (the step's own gc.collect() then scans only new objects)",
-            "dtypes": {"fp32": "reference default precision (tensor cores where the 1e-5 bound holds, SIMT FFMA elsewhere)",
+            "dtypes": {"fp32": "reference default precision (tensor cores, bf16 x3 split with the accumulation chains bounded for the 1e-5 bound; FFMA kernels where that is not possible)",
                        "fp32_tc": "fp32 tensors, every convolution on the tensor cores (bf16 x3 split, MK_F32_TC=2)",
                        "bf16": "torch.autocast(bf16) = Lightning bf16-mixed"},
             **out}

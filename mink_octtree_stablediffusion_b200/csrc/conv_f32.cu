@@ -30,6 +30,7 @@
 namespace mk {
 // conv_tc.cu / conv_wgrad_tc.cu
 bool conv_fwd_tc_eligible(int dtype, int64_t n_out, int K, int c_in, int c_out);
+void conv_fwd_tc_set_kper_max(int kper_max);
 int64_t conv_fwd_tc_workspace(int64_t n_out, int K, int c_in, int c_out);
 int conv_fwd_tc(int dtype, const void *x, const void *w, int transpose_w, int kflip, const int32_t *nbr,
                 const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
@@ -40,6 +41,7 @@ int conv_wgrad_tc(int dtype, const void *x, const void *dy, const int32_t *dy_ro
                   const uint32_t *tile_mask, int64_t ld, int64_t n_out, int64_t n_in, int K, int c_in, int c_out,
                   void *dw, void *workspace, cudaStream_t st, int dw_f32);
 int64_t conv_wgrad_tc_rows_per_cta(int64_t n_out, int K, int c_in, int c_out);
+void conv_wgrad_tc_set_rows_max(int64_t rows_max);
 
 namespace {
 
@@ -166,12 +168,34 @@ static int64_t chain_limit() {
   return e ? atoll(e) : 400;
 }
 
+// Offsets one accumulator may see under the chain limit (0 = no limit: "fast fp32"; -1 = not even one).
+// Beyond it the tensor-core kernel splits the offsets over grid.z and the partial outputs are added in
+// fp32 with round to nearest (conv_tc.cu, ksplit).
+static int kper_max_for(int c_in) {
+  const Terms t = terms();
+  if (f32_mode() >= 2) return 0;
+  const int64_t per_offset = (int64_t)(pad16(c_in) / 16) * t.n;      // MMAs one offset adds to the chain
+  const int64_t k = chain_limit() / per_offset;
+  return k >= 1 ? (int)std::min<int64_t>(k, 1 << 20) : -1;
+}
+struct KperGuard {
+  explicit KperGuard(int v) { conv_fwd_tc_set_kper_max(v); }
+  ~KperGuard() { conv_fwd_tc_set_kper_max(0); }
+};
+
+// the weight gradient's chain runs over the rows a CTA reduces (16 per MMA): bound them the same way
+struct RowsGuard {
+  RowsGuard() { conv_wgrad_tc_set_rows_max(f32_mode() >= 2 ? 0 : chain_limit() * 16); }
+  ~RowsGuard() { conv_wgrad_tc_set_rows_max(0); }
+};
+
 bool conv_fwd_f32_eligible(int64_t n_out, int K, int c_in, int c_out) {
   const Terms t = terms();
   const int mode = f32_mode();
   if (mode <= 0) return false;
-  const int64_t chain = (int64_t)K * (pad16(c_in) / 16) * t.n;        // MMAs into one accumulator
-  if (mode == 1 && chain > chain_limit()) return false;
+  const int kmax = kper_max_for(c_in);
+  if (kmax < 0) return false;
+  KperGuard g(kmax);
   return conv_fwd_tc_eligible(MK_BF16, n_out, K, t.n * pad16(c_in), pad16(c_out));
 }
 
@@ -180,15 +204,17 @@ bool conv_wgrad_f32_eligible(int64_t n_out, int K, int c_in, int c_out) {
   const int mode = f32_mode();
   if (mode <= 0) return false;
   const int cip = t.nw * pad16(c_in), cop = t.nw * pad16(c_out);
+  RowsGuard g;
   if (!conv_wgrad_tc_eligible(MK_BF16, n_out, K, cip, cop)) return false;
   // the reduction runs over the rows a CTA walks: 16 rows per MMA
-  const int64_t chain = conv_wgrad_tc_rows_per_cta(n_out, K, cip, cop) / 16 + 1;
+  const int64_t chain = conv_wgrad_tc_rows_per_cta(n_out, K, cip, cop) / 16;
   return mode >= 2 || chain <= chain_limit();
 }
 
 int64_t conv_fwd_f32_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out) {
   const Terms t = terms();
   const int cip = pad16(c_in), cop = pad16(c_out);
+  KperGuard g(std::max(0, kper_max_for(c_in)));
   return (int64_t)(al256((size_t)n_in * t.n * cip * 2) + al256((size_t)K * t.n * cip * cop * 2) +
                    (cop != c_out ? al256((size_t)n_out * cop * 4) : 0) +
                    (size_t)conv_fwd_tc_workspace(n_out, K, t.n * cip, cop) + 256);
@@ -197,6 +223,7 @@ int64_t conv_fwd_f32_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int
 int64_t conv_wgrad_f32_workspace(int64_t n_out, int64_t n_in, int K, int c_in, int c_out) {
   const Terms t = terms();
   const int cip = pad16(c_in), cop = pad16(c_out);
+  RowsGuard g;
   return (int64_t)(al256((size_t)n_in * t.nw * cip * 2) + al256((size_t)n_out * t.nw * cop * 2) +
                    al256((size_t)K * t.nw * cip * t.nw * cop * 4) +
                    (size_t)conv_wgrad_tc_workspace(n_out, K, t.nw * cip, t.nw * cop) + 256);
@@ -368,8 +395,12 @@ int conv_fwd_f32(const float *x, const float *w, int transpose_w, int kflip, con
   // W: [K, c_red = c_in, c_n = c_out] (transpose_w == 0) or [K, c_n = c_out, c_red = c_in]
   k_split_w<<<grid_for((int64_t)K * cip * cop, 256), 256, 0, st>>>(w, transpose_w, K, c_in, c_out, cip, cop, t.n, pb, b);
   MK_LAUNCH_CHECK();
-  int rc = conv_fwd_tc(MK_BF16, a, b, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, t.n * cip, cop, ypad,
-                       out_rows, ws, st, 1);
+  int rc;
+  {
+    KperGuard g(std::max(0, kper_max_for(c_in)));
+    rc = conv_fwd_tc(MK_BF16, a, b, transpose_w, kflip, nbr, tile_mask, ld, n_out, n_in, K, t.n * cip, cop, ypad,
+                     out_rows, ws, st, 1);
+  }
   if (rc) return rc;
   if (ypad != y) {
     k_unpad_cols<<<grid_for(n_out * c_out, 256), 256, 0, st>>>(ypad, n_out, c_out, cop, y);
@@ -394,6 +425,7 @@ int conv_wgrad_f32(const float *x, const float *dy, const int32_t *dy_rows, cons
   MK_LAUNCH_CHECK();
   k_split_rows<<<grid_for(n_out * (cop >> 3), 256), 256, 0, st>>>(dy, n_out, c_out, cop, t.nw, id, dys);
   MK_LAUNCH_CHECK();
+  RowsGuard g;
   int rc = conv_wgrad_tc(MK_BF16, xs, dys, dy_rows, nbr, tile_mask, ld, n_out, n_in, K, t.nw * cip, t.nw * cop, dw9, ws,
                          st, 1);
   if (rc) return rc;

@@ -922,6 +922,13 @@ struct TCPlan {
 
 static inline size_t align256s(size_t b) { return (b + 255) & ~(size_t)255; }
 
+// Upper bound on the offsets one accumulator may see (0 = none): set by the fp32 split path around its
+// calls (conv_f32.cu), whose bf16-piece products must not chain more than ~400 MMAs into one fp32
+// TMEM accumulator (tcgen05 accumulates with truncation); the plan then splits the offsets
+// over grid.z however many CTAs the layer has, and the partial outputs are added in fp32 (round to nearest).
+static thread_local int g_kper_max = 0;
+void conv_fwd_tc_set_kper_max(int kper_max) { g_kper_max = kper_max; }
+
 // One candidate: T tiles per group on accumulator halves `half_cols` apart (0 = a single set).
 static bool plan_with(int dtype, int64_t n_out, int K, int c_in, int c_out, int T, int half_cols, TCPlan &pl) {
   int nsplit = (c_out + 255) / 256;
@@ -980,9 +987,14 @@ static bool plan_with(int dtype, int64_t n_out, int K, int c_in, int c_out, int 
     if (ks >= 2) {
       pl.kper = (K + ks - 1) / ks;
       pl.ksplit = (K + pl.kper - 1) / pl.kper;
-      pl.part_bytes = align256s((size_t)pl.ksplit * n_out * c_out * 4);
     }
   }
+  if (dtype == MK_BF16 && g_kper_max > 0 && pl.kper > g_kper_max) {
+    pl.kper = g_kper_max;
+    pl.ksplit = (K + pl.kper - 1) / pl.kper;
+    if (pl.nsplit * pl.ksplit > 64) return false;   // one group counter per (offset split, output split)
+  }
+  if (pl.ksplit > 1) pl.part_bytes = align256s((size_t)pl.ksplit * n_out * c_out * 4);
   return true;
 }
 

@@ -581,6 +581,14 @@ static int arm_hang_report() {
   return MK_OK;
 }
 
+// Upper bound on the rows one CTA may reduce over (0 = none): set by the fp32 split path around its calls
+// (conv_f32.cu) - its bf16-piece products must not chain more than ~400 MMAs (16 rows each) into one fp32
+// TMEM accumulator (tcgen05 accumulates with truncation).  The plan then takes as many tile
+// splits as that needs, whatever the SM count (several waves of CTAs), and k_wgrad_reduce adds the
+// partials in fp32 (round to nearest).
+static thread_local int64_t g_rows_max = 0;
+void conv_wgrad_tc_set_rows_max(int64_t rows_max) { g_rows_max = rows_max; }
+
 namespace {
 struct WPlan {
   int pa, npairs, nsplit, NB, nbpad, pb, U, G, ppg, a_stages, b_bufs, ntiles, X, W;
@@ -622,6 +630,12 @@ bool make_wplan(int dtype, int64_t n_out, int K, int c_in, int c_out, WPlan &pl)
   pl.ntiles = (int)((n_out + kTileM - 1) / kTileM);
   const int ctas_y = pl.G * nsplit;
   pl.X = std::max(1, std::min(pl.ntiles, num_sms() / ctas_y));
+  if (g_rows_max > 0) {
+    const int tiles_max = (int)std::max<int64_t>(1, g_rows_max / kTileM);
+    pl.X = std::max(pl.X, (pl.ntiles + tiles_max - 1) / tiles_max);
+    if ((size_t)pl.X * K * c_in * c_out * 4 > ((size_t)8 << 30)) return false;   // partial sums beyond 8 GB: not served
+    if ((int64_t)pl.X * ctas_y > 0x7fff0000ll || ctas_y > 65535) return false;
+  }
   const size_t b_tile = (size_t)pl.pb * kPanelBytes;
   const size_t fixed = 1024 + (size_t)kIdxSlots * kTileM * 4 + 1024;
   const size_t budget = 227 * 1024;

@@ -46,11 +46,12 @@ def test_conv_fwd_bwd_same_map(dtype, cin, cout):
     tol = TOL[dtype]
     y = abi.conv_fwd(xd, wd, nbr, ld, n)
     assert rel_err(y.double().cpu().numpy(), y_ref) <= tol
-    # fp32 runs on the tensor cores too where the accumulation chain is short enough for 1e-5
-    # (bf16 operand splitting, channels padded to 16: conv_f32.cu); wide layers stay on the SIMT FFMA kernel
+    # fp32 runs on the tensor cores too (bf16 operand splitting, channels padded to 16: conv_f32.cu): the
+    # offsets are split over grid.z so that no accumulator chains more than ~400 MMAs (tcgen05 accumulates
+    # with truncation) and the partial outputs are added in fp32 - the 1e-5 bound below checks exactly that
     if abi.tc_eligible(dtype, n, 27, cin, cout):
         assert abi.last_path() == 1
-    assert abi.tc_eligible(torch.float32, n, 27, cin, cout) == (cin <= 32)
+    assert abi.tc_eligible(torch.float32, n, 27, cin, cout)
     if dtype == torch.float32:
         y_simt = abi.conv_fwd(xd, wd, nbr, ld, n, legacy=True)      # the SIMT kernel still serves the old entry point
         assert abi.last_path() == 0 and rel_err(y_simt.double().cpu().numpy(), y_ref) <= tol
@@ -324,6 +325,33 @@ def test_tensor_core_plans_agree_under_load(monkeypatch):
             assert torch.equal(run(), ref), T
 
 
+@pytest.mark.parametrize("cin,cout", [(256, 192), (512, 512)])
+def test_fp32_wide_layers_on_tensor_cores_keep_1e5(cin, cout):
+    """fp32 layers whose accumulation chain would exceed the ~400 MMAs a TMEM accumulator tolerates (tcgen05
+    adds with truncation): the split path bounds the chain - offsets split over grid.z for forward / data
+    gradient, more tile splits for the weight gradient - and adds the partials in fp32.  north_star's 1e-5
+    against the fp64 kernels (themselves checked against the oracle in test_conv_fwd_bwd_same_map)."""
+    c = _northstar_cloud(45, "sorted")
+    offs = O.kernel_offsets([3, 3, 3], [1, 1, 1])
+    tin = abi.insert(c)
+    nbr, ld, _ = abi.kmap_build(tin["coords_dev"], tin["table"], tin["cap"], offs)
+    n = len(c)
+    g = torch.Generator().manual_seed(41)
+    x = torch.randn(n, cin, generator=g, dtype=torch.float64).cuda()
+    w = (torch.randn(27, cin, cout, generator=g, dtype=torch.float64) / np.sqrt(27 * cin)).cuda()
+    dy = torch.randn(n, cout, generator=g, dtype=torch.float64).cuda()
+    xf, wf, dyf = x.float(), w.float(), dy.float()
+    x, w, dy = xf.double(), wf.double(), dyf.double()          # the reference sees the fp32-rounded values
+    assert abi.tc_eligible(torch.float32, n, 27, cin, cout)
+    rel = lambda a, b: float((a.double() - b).abs().max() / b.abs().max())
+    y = abi.conv_fwd(xf, wf, nbr, ld, n)
+    assert abi.last_path() == 1 and rel(y, abi.conv_fwd(x, w, nbr, ld, n)) <= 1e-5
+    gi = abi.conv_fwd(dyf, wf, nbr, ld, n, transpose_w=1, kflip=1)
+    assert abi.last_path() == 1 and rel(gi, abi.conv_fwd(dy, w, nbr, ld, n, transpose_w=1, kflip=1)) <= 1e-5
+    gw = abi.conv_wgrad(xf, dyf, nbr, ld, n, 27)
+    assert abi.last_path() == 1 and rel(gw, abi.conv_wgrad(x, dy, nbr, ld, n, 27)) <= 1e-5
+
+
 def test_gather_loop_forms_agree(monkeypatch):
     """The gather warps' three loop forms for Cin = 64, Cout <= 64, K <= 32 - the general loop
     (MK_TC_NOLEAN), the lean loop (default) and the lean loop with TMA tile::gather4 for the fully
@@ -358,7 +386,7 @@ def test_gather_loop_forms_agree(monkeypatch):
 
 
 @pytest.mark.parametrize("R,order,with_coords", [(60, "sorted", True), (60, "shuffled", True), (40, "sorted", False)])
-def test_tile_ordered_table(R, order, with_coords):
+def test_tile_ordered_table(R, order, with_coords, monkeypatch):
     """mk_kmap_tile_order: `order` is a permutation, the ordered table is the table with its
     columns permuted (bit-exact), it touches fewer (tile, offset) pairs, and the convolution on
     it (mk_conv_fwd_rows / dy gathered for the weight gradient) gives the same result: the
@@ -401,8 +429,10 @@ def test_tile_ordered_table(R, order, with_coords):
         abi.conv_fwd_rows(x.double(), w.double(), nbr_t, ld, n, perm)
     with pytest.raises(RuntimeError):
         abi.conv_wgrad(x.double(), dy.double(), nbr_t, ld, n, 27, dy_rows=perm)
-    # fp32 beyond the split path's accumulation limit: the tuned FFMA kernels honour the permutations too
+    # fp32 off the tensor cores (MK_F32_TC=0; by default only shapes the split path cannot serve): the tuned
+    # FFMA kernels honour the permutations too
     xf, wf, dyf = x.float(), w.float(), dy.float()
+    monkeypatch.setenv("MK_F32_TC", "0")
     assert not abi.tc_eligible(torch.float32, n, 27, 64, 64)
     s0 = abi.conv_fwd(xf, wf, nbr, ld, n)
     s1 = abi.conv_fwd_rows(xf, wf, nbr_t, ld, n, perm, mask=abi.tile_mask(nbr_t, n, ld, 27))
@@ -412,6 +442,7 @@ def test_tile_ordered_table(R, order, with_coords):
     v0 = abi.conv_wgrad(xf, dyf, nbr, ld, n, 27)
     v1 = abi.conv_wgrad(xf, dyf, nbr_t, ld, n, 27, dy_rows=perm)
     assert float((v0 - v1).abs().max() / v0.abs().max()) <= 1e-5
+    monkeypatch.delenv("MK_F32_TC")
     # fp32: where the split tensor-core path serves the shape it honours the permutations too
     x32, w32, dy32 = x.float()[:, :32].contiguous(), w.float()[:, :32].contiguous(), dy.float()
     if abi.tc_eligible(torch.float32, n, 27, 32, 64):
