@@ -61,7 +61,11 @@ constexpr int kPanelBytes = kTileM * 128;   // [128 rows x 64 ch] 16-bit
 constexpr int kStageBytes = 2 * kPanelBytes;
 constexpr int kGatherTeams = 4;
 constexpr int kGatherWarps = 4 * kGatherTeams;   // a team of 4 warps fills one panel (32 rows per warp)
-constexpr int kMmaWarps = 2;   // MMA warp m issues for the CTA's units u = m (mod 2): accumulators nobody else touches
+#ifndef MK_WG_MMA_WARPS
+#define MK_WG_MMA_WARPS 2
+#endif
+constexpr int kMmaWarps = MK_WG_MMA_WARPS;   // MMA warp m issues for the CTA's units u = m (mod kMmaWarps): accumulators nobody else touches
+static_assert(kMmaWarps == 2 || kMmaWarps == 4, "unit masks below are written for 2 or 4 issuing warps");
 constexpr int kWarpIdx = kGatherWarps, kWarpMma = kGatherWarps + 1, kWarpDy = kWarpMma + kMmaWarps;
 constexpr int kThreads = 32 * (kGatherWarps + 2 + kMmaWarps);
 constexpr int kIdxSlots = 32;
@@ -390,7 +394,7 @@ k_conv_wgrad_tc(const __grid_constant__ wg::Params p, const __grid_constant__ CU
     WP_DECL(m_wb = 0, m_wa = 0, m_is = 0, m_t0 = 0, m_start = 0;)
     WP_T0(m_start);
     const UnitConst uc = unit_const(p, g, npair_cta, lane);
-    const uint32_t mine_mask = 0x55555555u << mw;   // kMmaWarps == 2
+    const uint32_t mine_mask = (kMmaWarps == 2 ? 0x55555555u : 0x11111111u) << mw;
     uint32_t wn[4];
     load_mask(p, xs, wn);
     for (int tile = xs; tile < p.ntiles; tile += p.X) {
