@@ -2,6 +2,8 @@
 (pybind/extern.hpp:84-114,151-181,215-428,579-646) on the C-ABI library."""
 from __future__ import annotations
 
+import os
+
 import ctypes
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -258,7 +260,10 @@ _WS_BYTES: Dict[tuple, int] = {}
 
 
 def _workspace(lib, dtype_code, n_out, n_in, K, c_in, c_out, dev):
-    key = (dtype_code, n_out, n_in, K, c_in, c_out)
+    # (the fp32 policy knobs change what the library needs: they are part of the key)
+    env = os.environ
+    key = (dtype_code, n_out, n_in, K, c_in, c_out, env.get("MK_F32_TC"), env.get("MK_F32_TC_CHAIN"),
+           env.get("MK_F32_TERMS"), env.get("MK_TC_NOKSPLIT"), env.get("MK_WG_PREGATHER"), env.get("MK_WG_NB"))
     nbytes = _WS_BYTES.get(key)
     if nbytes is None:
         if len(_WS_BYTES) > 4096:
