@@ -444,9 +444,46 @@ def run_engine(args):
             raw[nm] = e_a.elapsed_time(e_b) / 10
         del tb_, ws_, ui_, iv_, co_
         K = KS ** 3
+        # the coordinate stages of the octree decoder / encoder on the same cloud, through the manager the
+        # ME API uses (SURVEY 8d bytes): stride-2 map, k2s2 generative children, pruning of half the rows
+        from mink_octtree_stablediffusion_b200 import backend_pool as _pool
+        sms_, exs_, prs_ = [], [], []
+        n_half = n_str = n_chl = 0
+        keep_ = (torch.arange(n, device=dev) % 2 == 0)
+        feat_ = torch.zeros((n, C_IN), dtype=torch.bfloat16, device=dev)
+        offs8 = np.array([[i, j, k_] for i in (0, 1) for j in (0, 1) for k_ in (0, 1)], dtype=np.int64)
+        for _ in range(5):
+            m3 = _C.CoordinateMapManagerGPU_c10()
+            k3, _ = m3.insert_and_map(coords_d, [1, 1, 1], "")
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+            torch.mm(busy, busy)
+            ev[0].record()
+            ks2 = m3.stride(k3, [2, 2, 2])
+            ev[1].record()
+            torch.mm(busy, busy)
+            ev[2].record()
+            kch = m3._octree_children(ks2, offs8, [1, 1, 1])
+            ev[3].record()
+            torch.mm(busy, busy)
+            ev[4].record()
+            okey = _C.CoordinateMapKey(4)
+            _pool.PruningForwardGPU(feat_, keep_, k3, okey, m3)
+            ev[5].record()
+            torch.cuda.synchronize()
+            sms_.append(ev[0].elapsed_time(ev[1]))
+            exs_.append(ev[2].elapsed_time(ev[3]))
+            prs_.append(ev[4].elapsed_time(ev[5]))
+            n_str, n_chl, n_half = m3.size(ks2), (m3.size(kch) if kch is not None else 0), m3.size(okey)
+        del feat_, keep_
         stage = {"hash_insert_ms": float(np.median(ins)), **raw, "kmap_build_ms": float(np.median(kmb)),
                  "kmap_pairs_export_ms": float(np.median(kme)), "kmap_tile_order_ms": float(np.median(kto)),
-                 "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n)}
+                 "hash_insert_alg_bytes": 84 * n, "kmap_alg_bytes": int((16 + 32 * K) * n),
+                 "stride_ms": float(np.median(sms_)), "stride_alg_bytes": int((16 + 84) * n + 16 * n_str),
+                 "expand_ms": float(np.median(exs_)), "expand_alg_bytes": int(16 * n_str + (16 + 84) * n_chl),
+                 "prune_ms": float(np.median(prs_)),
+                 "prune_alg_bytes": int((1 + 16 + 2 * C_IN) * n + (16 + 2 * C_IN + 84) * n_half),
+                 "stage_note": "stride / expand / prune are timed at the ME-manager level: each includes its output map's "
+                               "insert, allocations and (stride, prune) one count read-back"}
 
     # ---- wider layers of the same cloud (MinkUNet / VAE widths): tensor-bound there ----------
     wide, cfg1 = [], None
@@ -597,6 +634,8 @@ def run_engine(args):
             line["stages"]["hash_insert_hbm_frac"] = stage["hash_insert_alg_bytes"] / (stage["hash_insert_kernels_ms"] * 1e-3) / 1e9 / pk["hbm"]
             line["stages"]["hash_insert_api_hbm_frac"] = stage["hash_insert_alg_bytes"] / (stage["hash_insert_ms"] * 1e-3) / 1e9 / pk["hbm"]
             line["stages"]["kmap_hbm_frac"] = stage["kmap_alg_bytes"] / (stage["kmap_build_ms"] * 1e-3) / 1e9 / pk["hbm"]
+            for nm in ("stride", "expand", "prune"):
+                line["stages"][nm + "_hbm_frac"] = stage[nm + "_alg_bytes"] / (stage[nm + "_ms"] * 1e-3) / 1e9 / pk["hbm"]
         if world == 1 and not args.no_cpu_baseline:
             s = cpu_sample(96, 3)
             line["cpu_baseline"] = {"value": s["n"] / s["step_s"], "unit": UNIT, "cores": s["cores"], "kind": "port",
