@@ -234,3 +234,30 @@ def test_sparse_tensor_arithmetic_union():
     vals = {tuple(r): float(v) for r, v in zip(Ssum.C.cpu().numpy(), Ssum.F[:, 0].cpu().numpy())}
     for r in sa | sb:
         assert vals[r] == (1.0 if r in sa else 0.0) + (2.0 if r in sb else 0.0)
+
+
+def test_empty_and_single_voxel_tensors():
+    """Edge sizes through the ME API: pruning that keeps nothing gives an empty tensor that convolutions,
+    norms' parents and the backward pass accept (zero rows in, zero rows out, zero weight gradient), and a
+    single voxel convolves with its centre offset only."""
+    ME = _me()
+    c = torch.from_numpy(O.sphere_surface(9, 0, 0)).cuda()
+    n = len(c)
+    torch.manual_seed(3)
+    for dtype in (torch.float32, torch.bfloat16):
+        x = torch.randn(n, 16).to(dtype).cuda().requires_grad_(True)
+        st = ME.SparseTensor(x, c)
+        conv = ME.MinkowskiConvolution(16, 32, kernel_size=3, dimension=3).to(dtype).cuda()
+        pruned = ME.MinkowskiPruning()(st, torch.zeros(n, dtype=torch.bool, device="cuda"))
+        assert pruned.F.shape == (0, 16) and pruned.C.shape == (0, 4)
+        out = conv(pruned)
+        assert out.F.shape == (0, 32)
+        out.F.sum().backward()
+        assert conv.kernel.grad is not None and float(conv.kernel.grad.abs().max()) == 0.0
+        assert x.grad is not None and float(x.grad.abs().max()) == 0.0
+        # one voxel: only the centre offset has a neighbour
+        one = ME.SparseTensor(torch.ones(1, 16).to(dtype).cuda(), c[:1].contiguous())
+        y = conv(one)
+        want = conv.kernel.detach()[13].double().sum(dim=0)
+        assert y.F.shape == (1, 32)
+        assert float((y.F.detach().double()[0] - want).abs().max()) <= (1e-5 if dtype == torch.float32 else 5e-2)
