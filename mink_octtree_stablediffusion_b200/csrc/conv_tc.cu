@@ -950,10 +950,15 @@ static bool plan_with(int dtype, int64_t n_out, int K, int c_in, int c_out, int 
                  kSchedCopies * (size_t)((K + 31) & ~31) + 64 + 1024 /*barriers*/;
   const size_t budget = 227 * 1024;
   const size_t stage_bytes = (size_t)pl.T * kTileBytes;
-  if (fixed + 3 * stage_bytes > budget) return false;
+  // Four tiles on one accumulator set may run on a ring of TWO 64 KB stages (128 output columns: three do
+  // not fit beside the weight images).  What bounds these kernels is the MMA warps' fixed chain per stage
+  // (~1400 cycles), so a stage with twice the MMA work beats a deeper ring of small stages:
+  // 128 -> 128 forward 0.795 -> 0.645 ms against two tiles on each of two sets and five stages.
+  const int s_min = (T == 4 && half_cols == 0 && !getenv("MK_TC_S3")) ? 2 : 3;
+  if (fixed + s_min * stage_bytes > budget) return false;
   int S = (int)((budget - fixed) / stage_bytes);
   S = std::min(S, 12);   // tickets[] holds 16
-  if (S < 3 || S * pl.T <= 4) return false;   // producer teams: consecutive stages of a team must be < S apart
+  if (S < s_min || S * pl.T <= 4) return false;   // producer teams: consecutive stages of a team must be < S apart
   pl.a_stages = S;
   // Whatever is left after the A ring goes to the weight ring: with two images the copy of
   // the image for stage n+2 starts when stage n retires, one stage period before it is
@@ -1014,8 +1019,8 @@ static bool make_plan(int dtype, int64_t n_out, int K, int c_in, int c_out, TCPl
   // of weights re-read per 16 KB of gathered rows, and the SM ingests ~64 B/clk whatever the source).  One
   // set of up to 512 columns lets more tiles share an image; the price is that a group's first MMA waits for
   // the previous group's epilogue (a few thousand cycles per ~100 k cycles of MMA work at these widths).
-  // Taken when it at least doubles the tiles per image and the A ring still holds three stages (128 columns:
-  // four tiles do not fit the ring, and three on one set measured slower than two on each of two sets).
+  // Taken when it at least doubles the tiles per image and the A ring still holds three stages (two for
+  // four tiles, see plan_with; three tiles on one set measured slower than two on each of two sets).
   if (!getenv("MK_TC_TWO_SETS"))
     for (int t = t_one; t >= 2 * t_two; --t)
       if (plan_with(dtype, n_out, K, c_in, c_out, t, 0, pl)) return true;
