@@ -551,7 +551,7 @@ k_wgrad_reduce(const float *__restrict__ partial, int X, int64_t n, T *__restric
 
 // out[i, :] = dy[rows[i], :] (16-bit rows of `row_bytes`, a multiple of 16), 16 bytes per thread.
 // For wide outputs the weight-gradient kernel reads dy tiles with one tiled TMA load per panel from
-// this copy instead of 32 tile::gather4 per panel through the permutation: a CTA of a wide layer needs
+// this copy instead of 32 tile::gather4 per panel through the permutation: a CTA of a layer wider than 64 columns needs
 // a new dy tile every ~1300 cycles (few units per CTA, so few stages per tile), and the single loader
 // warp's gather4 stream took ~4500 (measured: 63 % of the MMA warps' time waiting for the dy tile at
 // 256 -> 256; 4.68 -> 3.2 ms + 0.2 ms for this pass).
@@ -602,7 +602,7 @@ struct WPlan {
 // dy through a tile order: pre-gathered copy (wide outputs) or tile::gather4 inside the kernel (narrow)
 inline bool pregather_dy(int c_out) {
   if (const char *e = getenv("MK_WG_PREGATHER")) return atoi(e) != 0;   // development knob
-  return c_out >= 128;
+  return c_out > 64;   // measured: 96 -> 96 1.03 -> 0.72 ms with the copy, 64 -> 64 0.306 -> 0.359 (one panel: gather4 keeps up)
 }
 
 inline size_t align256w(size_t b) { return (b + 255) & ~(size_t)255; }
