@@ -731,8 +731,11 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
         l0 = int(lib.mk_launch_count())
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        walls = []
         for _ in range(steps):
+            t_w = time.perf_counter()
             loss = step()
+            walls.append((time.perf_counter() - t_w) * 1e3)   # (the step reads its loss back: it ends synchronised)
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -745,7 +748,11 @@ def run_vae_leg(args, dist, rank, world, dev, lib, steps, warmup):
         ms = float(t.item())
         rec = {"steps_per_s": 1e3 / ms, "ms_per_step": ms, "samples_per_s": batch * world * 1e3 / ms,
                "voxels_per_s": n_vox * world * 1e3 / ms, "loss": float(loss), "engine_launches_per_step":
-               (int(lib.mk_launch_count()) - l0) // steps}
+               (int(lib.mk_launch_count()) - l0) // steps,
+               # host wall time of the individual steps on this rank: the step is host-bound, so a busy host
+               # core shows up as a few slow steps; steps_per_s above is the mean over all of them
+               "step_wall_ms": {"median": float(np.median(walls)), "min": float(np.min(walls)),
+                                "max": float(np.max(walls))}}
         if not args.no_vae_profile:
             # one more step on EVERY rank (it holds collectives); rank 0 records its kernels
             import contextlib
@@ -874,8 +881,8 @@ def main():
     ap.add_argument("--no-nets", action="store_true", help="skip the MinkUNet34C / diffusion UNet leg")
     ap.add_argument("--no-bind", action="store_true", help="do not bind the ranks to their GPUs' host cores")
     ap.add_argument("--no-vae-profile", action="store_true")
-    ap.add_argument("--vae-steps", type=int, default=10)
-    ap.add_argument("--vae-warmup", type=int, default=3)
+    ap.add_argument("--vae-steps", type=int, default=20)
+    ap.add_argument("--vae-warmup", type=int, default=5)
     ap.add_argument("--vae-res", type=int, default=128)
     ap.add_argument("--vae-batch", type=int, default=16)
     ap.add_argument("--vae-dtypes", default="bf16,fp32_tc,fp32")
